@@ -1,0 +1,156 @@
+"""Seeded synthetic inputs for tests and benchmarks (no dataset, no network).
+
+* ``synthetic_tiles``       — uint8 HWC "whole-slide" tiles (1536x1536x3 by default)
+* ``synthetic_state_dict``  — a checkpoint in the reference's ``.pth`` key layout
+* ``synthetic_predictions`` — decoded head output ``[B, N, 5+C]`` for NMS stress
+                               
+* ``synthetic_detections``  — post-NMS rows for the box-merging step
+
+Only numpy/torch; used by the product-side bench and by tests alike.
+"""
+import numpy as np
+import torch
+
+GRIDS_416 = (13, 26, 52)
+ANCHORS_V3 = {13: ((116, 90), (156, 198), (373, 326)),
+              26: ((30, 61), (62, 45), (59, 119)),
+              52: ((10, 13), (16, 30), (33, 23))}
+
+
+def synthetic_tiles(batch, size=1536, seed=0xA11CE, first_tile=0):
+    """uint8 [batch, size, size, 3]; tile t depends only on (seed, first_tile+t).
+    Smooth low-frequency field plus blobs so BatchNorm statistics stay sane."""
+    out = np.empty((batch, size, size, 3), dtype=np.uint8)
+    yy, xx = np.meshgrid(np.arange(size, dtype=np.float32), np.arange(size, dtype=np.float32), indexing="ij")
+    for b in range(batch):
+        rng = np.random.default_rng([seed, first_tile + b])
+        img = np.full((size, size, 3), 200.0, dtype=np.float32)
+        img += 20.0 * np.sin(xx / rng.uniform(40, 200) + rng.uniform(0, 6))[..., None]
+        img += 15.0 * np.cos(yy / rng.uniform(40, 200) + rng.uniform(0, 6))[..., None]
+        for _ in range(int(rng.integers(4, 14))):
+            cx, cy = rng.uniform(0, size, 2)
+            r = rng.uniform(15, 120)
+            blob = np.exp(-((xx - cx) ** 2 + (yy - cy) ** 2) / (2 * r * r))
+            img -= blob[..., None] * rng.uniform(40, 140, 3).astype(np.float32)
+        img += rng.normal(0, 6, img.shape).astype(np.float32)
+        out[b] = np.clip(img, 0, 255).astype(np.uint8)
+    return out
+
+
+def synthetic_tiles_fast(batch, size=1536, seed=0xA11CE, first_tile=0):
+    """Cheaper variant for large benchmark batches: uniform random bytes
+    (FLOPs and bytes of the path do not depend on content)."""
+    rng = np.random.default_rng([seed, first_tile, batch])
+    return rng.integers(0, 256, size=(batch, size, size, 3), dtype=np.uint8)
+
+
+def synthetic_state_dict(model, seed=0, conf_bias=None):
+    """Fill ``model`` (a Darknet module) with the seeded synthetic checkpoint of
+    SURVEY.md §8c and return its state_dict: conv N(0,0.02) scaled up so that
+    activations neither die nor explode over 75 layers, BN gamma N(1,0.02),
+    beta small, running stats randomised so BN folding is exercised, head
+    objectness biases set from ``conf_bias`` so that a controllable fraction of
+    rows clears the confidence threshold."""
+    g = torch.Generator().manual_seed(seed)
+    sd = model.state_dict()
+    defs = model.module_defs
+    for key, t in sd.items():
+        leaf = key.rsplit(".", 1)[1]
+        layer = int(key.split(".")[1])
+        nxt = defs[layer + 1]["type"] if layer + 1 < len(defs) else ""
+        if "conv_" in key and leaf == "weight":
+            fan_in = t[0].numel()
+            gain = 2.0 / 1.01                       # variance-preserving for leaky(0.1)
+            if nxt == "shortcut":
+                gain *= 0.1                         # keep the residual stream from exploding
+            if nxt == "yolo":
+                gain = 1.5                          # raw head outputs of order 1
+            t.copy_(torch.randn(t.shape, generator=g) * (gain / fan_in) ** 0.5)
+        elif "conv_" in key and leaf == "bias":
+            t.copy_(torch.randn(t.shape, generator=g) * 0.3)
+        elif "batch_norm_" in key and leaf == "weight":
+            t.copy_(1.0 + 0.02 * torch.randn(t.shape, generator=g))
+        elif "batch_norm_" in key and leaf == "bias":
+            t.copy_(0.05 * torch.randn(t.shape, generator=g))
+        elif leaf == "running_mean":
+            t.copy_(0.1 * torch.randn(t.shape, generator=g))
+        elif leaf == "running_var":
+            t.copy_(0.5 + torch.rand(t.shape, generator=g))
+        elif leaf == "num_batches_tracked":
+            t.fill_(105)
+    if conf_bias is not None:
+        for key, t in sd.items():
+            if "conv_" in key and key.endswith(".bias"):
+                per_anchor = t.numel() // 3
+                for a in range(3):
+                    t[a * per_anchor + 4] = conf_bias
+    model.load_state_dict(sd)
+    return model.state_dict()
+
+
+def synthetic_predictions(batch, num_classes=2, seed=5, img=416, grids=GRIDS_416,
+                          clusters=(200, 400), anchors=None):
+    """Decoded predictions laid out like the real head: for each grid G (coarse
+    to fine) and anchor a, rows a*G*G + gy*G + gx; centres near the cell centre,
+    sizes = anchor * exp(N(0,0.3)); a few hundred planted object clusters so
+    that IoU>0.4 groups of 2..60 rows exist; conf ~ U(0.01,1), cls ~ U(0,1)^C;
+    scores conf*max(cls) made distinct within a tile (reference tie order is
+    unspecified)."""
+    anchors = anchors or ANCHORS_V3
+    rng = np.random.default_rng(seed)
+    n_rows = sum(3 * g * g for g in grids)
+    out = np.empty((batch, n_rows, 5 + num_classes), dtype=np.float32)
+    for b in range(batch):
+        rows = []
+        for g in grids:
+            stride = img / g
+            gy, gx = np.meshgrid(np.arange(g), np.arange(g), indexing="ij")
+            for a in range(3):
+                aw, ah = anchors[g][a] if g in anchors else (stride * 2, stride * 2)
+                cx = (gx.reshape(-1) + 0.5 + rng.uniform(-0.5, 0.5, g * g)) * stride
+                cy = (gy.reshape(-1) + 0.5 + rng.uniform(-0.5, 0.5, g * g)) * stride
+                w = aw * np.exp(rng.normal(0, 0.3, g * g))
+                h = ah * np.exp(rng.normal(0, 0.3, g * g))
+                rows.append(np.stack([cx, cy, w, h], 1))
+        box = np.concatenate(rows, 0)
+        n_clusters = int(rng.integers(clusters[0], clusters[1] + 1))
+        for _ in range(n_clusters):
+            size = int(rng.integers(2, 61))
+            members = rng.choice(n_rows, size=size, replace=False)
+            centre = rng.uniform(0, img, 2)
+            wh = rng.uniform(12, 160, 2)
+            box[members, 0:2] = centre + rng.normal(0, 0.04, (size, 2)) * wh
+            box[members, 2:4] = wh * np.exp(rng.normal(0, 0.06, (size, 2)))
+        conf = rng.uniform(0.01, 1.0, n_rows)
+        cls = rng.uniform(0.0, 1.0, (n_rows, num_classes))
+        p = np.concatenate([box, conf[:, None], cls], 1).astype(np.float32)
+        for _ in range(64):
+            score = p[:, 4] * p[:, 5:].max(1)
+            _, first, counts = np.unique(score, return_index=True, return_counts=True)
+            if (counts == 1).all():
+                break
+            dup = np.setdiff1d(np.arange(n_rows), first)
+            p[dup, 4] = rng.uniform(0.01, 1.0, dup.size).astype(np.float32)
+        out[b] = p
+    return out
+
+
+def synthetic_detections(count, seed=0, extent=1536.0, num_classes=2, overlap=0.5):
+    """Post-NMS rows [count,7] (x1,y1,x2,y2,conf,cls_conf,cls_pred) in original
+    tile coordinates, with a tunable share of overlapping same-class pairs and
+    some boxes hanging over the top/left edge (negative coordinates)."""
+    rng = np.random.default_rng(seed)
+    rows = np.zeros((count, 7), dtype=np.float32)
+    for i in range(count):
+        if i and rng.random() < overlap:
+            j = int(rng.integers(0, i))
+            cx = (rows[j, 0] + rows[j, 2]) / 2 + rng.normal(0, 40)
+            cy = (rows[j, 1] + rows[j, 3]) / 2 + rng.normal(0, 40)
+            cls = rows[j, 6] if rng.random() < 0.8 else float(rng.integers(0, num_classes))
+        else:
+            cx, cy = rng.uniform(-20, extent + 20, 2)
+            cls = float(rng.integers(0, num_classes))
+        w, h = rng.uniform(20, 260, 2)
+        rows[i] = (cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2,
+                   rng.uniform(0.8, 1.0), rng.uniform(0.5, 1.0), cls)
+    return rows
