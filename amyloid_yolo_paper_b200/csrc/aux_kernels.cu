@@ -1,0 +1,368 @@
+// Bandwidth-bound helper kernels around the tensor-core convolution:
+//   first_conv      Cin=3 first layer, with ToTensor(/255) + nearest Resize fused
+//                   (utils/transforms.py:89-111, models.py:26-45 layer 0)
+//   s2_gather       parity planes feeding stride-2 3x3 convolutions
+//   upsample2       nearest x2 into a channel slice of a concat buffer (models.py:86-96, 244-245)
+//   maxpool         2x2 s2 and 2x2 s1 (+ZeroPad right/bottom) for yolov3-tiny (models.py:47-53)
+//   add             stand-alone shortcut (models.py:246-248) when it cannot be fused
+//   dump_nchw       test helper: padded NHWC 16-bit -> NCHW fp32
+//   ref_conv        CUDA-core direct convolution, test cross-check of the tcgen05 kernel
+//   decode          stand-alone YOLO decode (models.py:137-169) used with ref_conv
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "ay_common.h"
+
+namespace ay {
+namespace {
+
+__device__ __forceinline__ float ld16(const void* base, size_t idx, int is_fp16) {
+  if (is_fp16) return __half2float(static_cast<const __half*>(base)[idx]);
+  return __bfloat162float(static_cast<const __nv_bfloat16*>(base)[idx]);
+}
+
+__device__ __forceinline__ uint16_t cvt16(float v, int is_fp16) {
+  if (is_fp16) {
+    __half h = __float2half_rn(v);
+    return *reinterpret_cast<uint16_t*>(&h);
+  }
+  __nv_bfloat16 b = __float2bfloat16_rn(v);
+  return *reinterpret_cast<uint16_t*>(&b);
+}
+
+__device__ __forceinline__ uint32_t pack16(float lo, float hi, int is_fp16) {
+  return (uint32_t)cvt16(lo, is_fp16) | ((uint32_t)cvt16(hi, is_fp16) << 16);
+}
+
+// ---------------------------------------------------------------- first conv
+// One thread per padded output pixel; all output channels in registers, 32 at a time.
+// Arithmetic in fp32 on fp32 weights (this layer is 0.5 % of the FLOPs and HBM-bound).
+__global__ void first_conv_kernel(FirstConvParams p) {
+  extern __shared__ float sw[];  // [cout][27] then bias[cout]
+  const int nw = p.cout * 27;
+  for (int i = threadIdx.x; i < nw + p.cout; i += blockDim.x) sw[i] = (i < nw) ? p.w[i] : p.bias[i - nw];
+  __syncthreads();
+  const int Sp = p.S + 2;
+  const long long total = (long long)p.batch * Sp * Sp;
+  const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= total) return;
+  const int n = (int)(m / ((long long)Sp * Sp));
+  const int pix = (int)(m - (long long)n * Sp * Sp);
+  const int y = pix / Sp, x = pix - y * Sp;
+  uint16_t* orow = static_cast<uint16_t*>(p.out) + (size_t)m * p.out_pitch;
+  const bool halo = (y == 0) | (y == Sp - 1) | (x == 0) | (x == Sp - 1);
+  if (halo) {
+    for (int c = 0; c < p.Cp; c += 8) *reinterpret_cast<uint4*>(orow + c) = make_uint4(0, 0, 0, 0);
+    return;
+  }
+  float in[27];
+#pragma unroll
+  for (int kh = 0; kh < 3; ++kh) {
+#pragma unroll
+    for (int kw = 0; kw < 3; ++kw) {
+      const int iy = y - 1 + kh - 1, ix = x - 1 + kw - 1;
+      const bool ok = (iy >= 0) & (iy < p.S) & (ix >= 0) & (ix < p.S);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float v = 0.f;
+        if (ok) {
+          if (p.in_kind == AY_IN_F32_NCHW) {
+            v = __ldg(static_cast<const float*>(p.in) + (((size_t)n * 3 + c) * p.S + iy) * p.S + ix);
+          } else {
+            const int sy = __ldg(p.idx_y + iy), sx = __ldg(p.idx_x + ix);
+            const uint8_t u = __ldg(static_cast<const uint8_t*>(p.in) +
+                                    (((size_t)n * p.src_h + sy) * p.src_w + sx) * 3 + c);
+            v = __fdiv_rn((float)u, 255.0f);
+          }
+        }
+        in[(kh * 3 + kw) * 3 + c] = v;
+      }
+    }
+  }
+  for (int oc0 = 0; oc0 < p.Cp; oc0 += 8) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int oc = oc0 + j;
+      float a = 0.f;
+      if (oc < p.cout) {
+        const float* w = sw + oc * 27;
+#pragma unroll
+        for (int k = 0; k < 27; ++k) a = fmaf(in[k], w[k], a);
+        a += sw[nw + oc];
+        if (p.leaky) a = a > 0.f ? a : 0.1f * a;
+      }
+      acc[j] = a;
+    }
+    *reinterpret_cast<uint4*>(orow + oc0) =
+        make_uint4(pack16(acc[0], acc[1], p.is_fp16), pack16(acc[2], acc[3], p.is_fp16),
+                   pack16(acc[4], acc[5], p.is_fp16), pack16(acc[6], acc[7], p.is_fp16));
+  }
+}
+
+// ---------------------------------------------------------------- stride-2 gather
+// planes[pl][n][a][b][:] = in[n][2(a-1)+ph][2(b-1)+pw][:]  (padded input coords; zero when
+// out of range), a in [0,Ho+2), b in [0,Wo+2), pl = ph*2+pw.  Output tap (kh,kw) of padded
+// output row m is then row  pl*plane_rows + m + (kh>>1)*(Wo+2) + (kw>>1).
+__global__ void s2_gather_kernel(const uint4* __restrict__ in, int in_pitch8, int C8, int batch, int H, int W,
+                                 uint4* __restrict__ planes, long long plane_rows) {
+  const int Ho = H / 2, Wo = W / 2;
+  const int Hq = Ho + 2, Wq = Wo + 2, Hp = H + 2, Wp = W + 2;
+  const long long per_plane = (long long)batch * Hq * Wq * C8;
+  const long long total = 4 * per_plane;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int pl = (int)(i / per_plane);
+    long long r = i - (long long)pl * per_plane;
+    const int c = (int)(r % C8);
+    r /= C8;
+    const int b = (int)(r % Wq);
+    r /= Wq;
+    const int a = (int)(r % Hq);
+    const int n = (int)(r / Hq);
+    const int iy = 2 * (a - 1) + (pl >> 1), ix = 2 * (b - 1) + (pl & 1);
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (iy >= 0 && iy < Hp && ix >= 0 && ix < Wp)
+      v = __ldg(in + ((size_t)((size_t)n * Hp + iy) * Wp + ix) * in_pitch8 + c);
+    planes[((size_t)pl * plane_rows + ((size_t)n * Hq + a) * Wq + b) * C8 + c] = v;
+  }
+}
+
+// ---------------------------------------------------------------- upsample x2 (nearest)
+__global__ void upsample2_kernel(const uint4* __restrict__ in, int in_pitch8, int C8, int batch, int H, int W,
+                                 uint4* __restrict__ out, int out_pitch8) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const long long total = (long long)batch * (Ho + 2) * (Wo + 2) * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C8);
+    long long r = i / C8;
+    const int x = (int)(r % (Wo + 2));
+    r /= (Wo + 2);
+    const int y = (int)(r % (Ho + 2));
+    const int n = (int)(r / (Ho + 2));
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (y >= 1 && y <= Ho && x >= 1 && x <= Wo) {
+      const int sy = ((y - 1) >> 1) + 1, sx = ((x - 1) >> 1) + 1;
+      v = __ldg(in + ((size_t)((size_t)n * (H + 2) + sy) * (W + 2) + sx) * in_pitch8 + c);
+    }
+    out[((size_t)((size_t)n * (Ho + 2) + y) * (Wo + 2) + x) * out_pitch8 + c] = v;
+  }
+}
+
+// ---------------------------------------------------------------- maxpool 2x2
+__global__ void maxpool_kernel(const void* __restrict__ in, int in_pitch, int Cp, int batch, int H, int W, int stride,
+                               void* __restrict__ out, int out_pitch, int is_fp16) {
+  const int Ho = (stride == 2) ? H / 2 : H, Wo = (stride == 2) ? W / 2 : W;
+  const long long total = (long long)batch * (Ho + 2) * (Wo + 2) * Cp;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % Cp);
+    long long r = i / Cp;
+    const int x = (int)(r % (Wo + 2));
+    r /= (Wo + 2);
+    const int y = (int)(r % (Ho + 2));
+    const int n = (int)(r / (Ho + 2));
+    float v = 0.f;
+    if (y >= 1 && y <= Ho && x >= 1 && x <= Wo) {
+      // padded input coordinates of the window's top-left element; the zero halo supplies the
+      // ZeroPad2d((0,1,0,1)) of the stride-1 variant (models.py:50-51)
+      const int iy = (stride == 2) ? 2 * (y - 1) + 1 : y, ix = (stride == 2) ? 2 * (x - 1) + 1 : x;
+      const size_t base = ((size_t)n * (H + 2) + iy) * (W + 2) + ix;
+      const float a = ld16(in, base * in_pitch + c, is_fp16);
+      const float b = ld16(in, (base + 1) * in_pitch + c, is_fp16);
+      const float d = ld16(in, (base + (W + 2)) * in_pitch + c, is_fp16);
+      const float e = ld16(in, (base + (W + 2) + 1) * in_pitch + c, is_fp16);
+      v = fmaxf(fmaxf(a, b), fmaxf(d, e));
+    }
+    static_cast<uint16_t*>(out)[(((size_t)n * (Ho + 2) + y) * (Wo + 2) + x) * out_pitch + c] = cvt16(v, is_fp16);
+  }
+}
+
+// ---------------------------------------------------------------- add / copy
+__global__ void add_kernel(const void* __restrict__ a, int a_pitch, const void* __restrict__ b, int b_pitch, int Cp,
+                           long long rows, void* __restrict__ out, int out_pitch, int is_fp16) {
+  const long long total = rows * Cp;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / Cp;
+    const int c = (int)(i - r * Cp);
+    const float v = ld16(a, (size_t)r * a_pitch + c, is_fp16) + ld16(b, (size_t)r * b_pitch + c, is_fp16);
+    static_cast<uint16_t*>(out)[(size_t)r * out_pitch + c] = cvt16(v, is_fp16);
+  }
+}
+
+__global__ void copy_channels_kernel(const uint4* __restrict__ in, int in_pitch8, int C8, long long rows,
+                                     uint4* __restrict__ out, int out_pitch8) {
+  const long long total = rows * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / C8;
+    const int c = (int)(i - r * C8);
+    out[(size_t)r * out_pitch8 + c] = __ldg(in + (size_t)r * in_pitch8 + c);
+  }
+}
+
+// ---------------------------------------------------------------- dump
+__global__ void dump_nchw_kernel(const void* __restrict__ in, int in_pitch, int C, int batch, int H, int W, int is_fp16,
+                                 float* __restrict__ out) {
+  const long long total = (long long)batch * C * H * W;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W);
+    long long r = i / W;
+    const int y = (int)(r % H);
+    r /= H;
+    const int c = (int)(r % C);
+    const int n = (int)(r / C);
+    out[i] = ld16(in, (((size_t)n * (H + 2) + y + 1) * (W + 2) + x + 1) * in_pitch + c, is_fp16);
+  }
+}
+
+// ---------------------------------------------------------------- reference conv (CUDA cores)
+__global__ void ref_conv_kernel(RefConvParams p) {
+  const int Hq = p.Ho + 2, Wq = p.Wo + 2, Hp = p.H + 2, Wp = p.W + 2;
+  const long long total = (long long)p.batch * Hq * Wq * p.cout_p;
+  const int pad = (p.size - 1) / 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int oc = (int)(i % p.cout_p);
+    long long m = i / p.cout_p;
+    const int x = (int)(m % Wq);
+    const int y = (int)((m / Wq) % Hq);
+    const int n = (int)(m / ((long long)Wq * Hq));
+    const bool halo = (y == 0) | (y == Hq - 1) | (x == 0) | (x == Wq - 1);
+    float acc = 0.f;
+    if (!halo) {
+      for (int kh = 0; kh < p.size; ++kh)
+        for (int kw = 0; kw < p.size; ++kw) {
+          // unpadded input coordinate, then +1 for the halo
+          const int iy = (y - 1) * p.stride + kh - pad + 1, ix = (x - 1) * p.stride + kw - pad + 1;
+          if (iy < 0 || iy >= Hp || ix < 0 || ix >= Wp) continue;
+          const size_t irow = ((size_t)n * Hp + iy) * Wp + ix;
+          const size_t wrow = (size_t)oc * p.ktot + (size_t)(kh * p.size + kw) * p.Cin_p;
+          for (int c = 0; c < p.Cin_p; ++c)
+            acc = fmaf(ld16(p.in, irow * p.in_pitch + c, p.is_fp16), ld16(p.w, wrow + c, p.is_fp16), acc);
+        }
+      acc += p.bias[oc];
+      if (p.leaky) acc = acc > 0.f ? acc : 0.1f * acc;
+      if (p.residual) acc += ld16(p.residual, (size_t)m * p.res_pitch + oc, p.is_fp16);
+    }
+    if (p.raw_f32) p.raw_f32[(size_t)m * p.cout_p + oc] = acc;
+    else static_cast<uint16_t*>(p.out)[(size_t)m * p.out_pitch + oc] = cvt16(acc, p.is_fp16);
+  }
+}
+
+__device__ __forceinline__ float sigmoidf_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__global__ void decode_kernel(DecodeParams p) {
+  const int Gq = p.G + 2;
+  const int cout = p.n_anchors * p.dec_cols;
+  const long long total = (long long)p.batch * p.G * p.G * cout;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int ch = (int)(i % cout);
+    long long r = i / cout;
+    const int gx = (int)(r % p.G);
+    const int gy = (int)((r / p.G) % p.G);
+    const int n = (int)(r / ((long long)p.G * p.G));
+    const size_t m = ((size_t)n * Gq + gy + 1) * Gq + gx + 1;
+    const float t = p.raw[m * p.raw_pitch + ch];
+    const int a = ch / p.dec_cols, f = ch - a * p.dec_cols;
+    float v;
+    if (f == 0) v = __fmul_rn(__fadd_rn(sigmoidf_acc(t), (float)gx), p.stride);
+    else if (f == 1) v = __fmul_rn(__fadd_rn(sigmoidf_acc(t), (float)gy), p.stride);
+    else if (f == 2) v = __fmul_rn(__fmul_rn(expf(t), p.anchor_w[a]), p.stride);
+    else if (f == 3) v = __fmul_rn(__fmul_rn(expf(t), p.anchor_h[a]), p.stride);
+    else v = sigmoidf_acc(t);
+    p.dec_out[(((size_t)n * p.dec_rows_total + p.dec_row_off) + (size_t)a * p.G * p.G + (size_t)gy * p.G + gx) *
+                  p.dec_cols + f] = v;
+  }
+}
+
+inline int grid_for(long long total, int block = 256) {
+  long long g = (total + block - 1) / block;
+  const long long cap = 148LL * 32;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+int launch_first_conv(const FirstConvParams& p, cudaStream_t s) {
+  const long long total = (long long)p.batch * (p.S + 2) * (p.S + 2);
+  const int block = 128;
+  const long long grid = (total + block - 1) / block;
+  const size_t smem = (size_t)(p.cout * 28) * sizeof(float);
+  first_conv_kernel<<<(unsigned)grid, block, smem, s>>>(p);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_s2_gather(const void* in, int in_pitch, int C8, int batch, int H, int W, void* planes,
+                     long long plane_rows, cudaStream_t s) {
+  const long long total = 4LL * batch * (H / 2 + 2) * (W / 2 + 2) * C8;
+  s2_gather_kernel<<<grid_for(total), 256, 0, s>>>(static_cast<const uint4*>(in), in_pitch / 8, C8, batch, H, W,
+                                                   static_cast<uint4*>(planes), plane_rows);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_upsample2(const void* in, int in_pitch, int Cp, int batch, int H, int W, void* out, int out_pitch,
+                     cudaStream_t s) {
+  const long long total = (long long)batch * (2 * H + 2) * (2 * W + 2) * (Cp / 8);
+  upsample2_kernel<<<grid_for(total), 256, 0, s>>>(static_cast<const uint4*>(in), in_pitch / 8, Cp / 8, batch, H, W,
+                                                   static_cast<uint4*>(out), out_pitch / 8);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_maxpool(const void* in, int in_pitch, int Cp, int batch, int H, int W, int size, int stride, void* out,
+                   int out_pitch, int is_fp16, cudaStream_t s) {
+  if (size != 2 || (stride != 1 && stride != 2) || (stride == 2 && ((H | W) & 1))) {
+    set_error("maxpool: only 2x2 stride 1/2 on even sizes is supported (size=%d stride=%d %dx%d)", size, stride, H, W);
+    return AY_EINVAL;
+  }
+  const int Ho = stride == 2 ? H / 2 : H, Wo = stride == 2 ? W / 2 : W;
+  const long long total = (long long)batch * (Ho + 2) * (Wo + 2) * Cp;
+  maxpool_kernel<<<grid_for(total), 256, 0, s>>>(in, in_pitch, Cp, batch, H, W, stride, out, out_pitch, is_fp16);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_add(const void* a, int a_pitch, const void* b, int b_pitch, int Cp, long long rows, void* out,
+               int out_pitch, int is_fp16, cudaStream_t s) {
+  add_kernel<<<grid_for(rows * Cp), 256, 0, s>>>(a, a_pitch, b, b_pitch, Cp, rows, out, out_pitch, is_fp16);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_copy_channels(const void* in, int in_pitch, int Cp, long long rows, void* out, int out_pitch,
+                         cudaStream_t s) {
+  copy_channels_kernel<<<grid_for(rows * (Cp / 8)), 256, 0, s>>>(static_cast<const uint4*>(in), in_pitch / 8, Cp / 8,
+                                                                 rows, static_cast<uint4*>(out), out_pitch / 8);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_dump_nchw(const void* in, int in_pitch, int C, int batch, int H, int W, int is_fp16, float* out,
+                     cudaStream_t s) {
+  dump_nchw_kernel<<<grid_for((long long)batch * C * H * W), 256, 0, s>>>(in, in_pitch, C, batch, H, W, is_fp16, out);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_ref_conv(const RefConvParams& p, cudaStream_t s) {
+  const long long total = (long long)p.batch * (p.Ho + 2) * (p.Wo + 2) * p.cout_p;
+  ref_conv_kernel<<<grid_for(total), 256, 0, s>>>(p);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_decode(const DecodeParams& p, cudaStream_t s) {
+  const long long total = (long long)p.batch * p.G * p.G * p.n_anchors * p.dec_cols;
+  decode_kernel<<<grid_for(total), 256, 0, s>>>(p);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+}  // namespace ay

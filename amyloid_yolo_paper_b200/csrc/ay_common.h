@@ -1,0 +1,128 @@
+// Shared declarations of the sm_100a tile-detection engine (internal; the public
+// C ABI is include/amyloid_yolo.h).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/amyloid_yolo.h"
+
+namespace ay {
+
+void set_error(const char* fmt, ...);
+
+#define AY_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      ay::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__,     \
+                    __LINE__);                                                            \
+      return AY_ECUDA;                                                                    \
+    }                                                                                     \
+  } while (0)
+
+// ---------------------------------------------------------------------------
+// Activations: zero-haloed NHWC, 16-bit.  A tensor of logical shape [B,C,H,W]
+// is stored as rows of `pitch` elements, one row per PADDED pixel
+//   row(n, y, x) = (n*(H+2) + y)*(W+2) + x,   y in [0,H+2), x in [0,W+2)
+// with the one-pixel halo (y==0, y==H+1, x==0, x==W+1) and channels >= C held at
+// zero.  A 3x3/stride-1 tap (kh,kw) of output row m is then input row
+// m + (kh-1)*(W+2) + (kw-1): every convolution becomes a GEMM over shifted rows.
+// ---------------------------------------------------------------------------
+struct ActView {
+  void* ptr = nullptr;   // element (0,0,0, channel 0) of this view
+  int C = 0;             // logical channels of the view
+  int Cp = 0;            // channels rounded up to a multiple of 32 (GEMM K granularity)
+  int H = 0, W = 0;      // unpadded spatial size
+  int pitch = 0;         // elements between consecutive pixels
+  long long rows_alloc = 0;  // pixel rows allocated behind ptr (for max_batch)
+};
+
+// Parameters of one implicit-GEMM convolution launch (conv_gemm_sm100.cu).
+struct ConvGemmParams {
+  int P;                 // output rows to compute: batch * (H+2) * (W+2)
+  int num_m_tiles;       // ceil(P / 128)
+  int num_n_tiles;       // ceil(Cout_padded / BN)
+  int n_taps;            // 1 or 9
+  int kb_per_tap;        // Cin_padded / BK
+  int a_row_off[9];      // row offset of tap t in the A matrix
+  int BN, BK;            // tile sizes (BK 64 -> 128B swizzle, 32 -> 64B swizzle)
+  int num_stages;
+  int Hp, Wp;            // padded output size (halo test)
+  int out_pitch;         // elements
+  void* out;             // 16-bit output rows (channel offset already applied)
+  const float* bias;     // [num_n_tiles*BN]
+  const void* residual;  // 16-bit rows or nullptr
+  int res_pitch;
+  int leaky;
+  int is_fp16;
+  // fused YOLO decode (head convolutions)
+  int head;
+  float* dec_out;        // [B, dec_rows_total, dec_cols]
+  int dec_rows_total, dec_row_off, dec_cols, n_anchors, cout;
+  float stride;
+  float anchor_w[8], anchor_h[8];   // already divided by stride (models.py:122)
+  unsigned int* err_flag;
+};
+
+int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p,
+                     int num_sms, cudaStream_t stream);
+int conv_gemm_smem_bytes(int BN, int BK, int stages);
+int conv_gemm_pick_stages(int BN, int BK);
+
+// aux_kernels.cu ------------------------------------------------------------
+struct FirstConvParams {
+  const void* in; int in_kind; int batch; int S; int src_h, src_w;
+  const int* idx_y; const int* idx_x;      // nearest-resize source indices (u8 input)
+  const float* w;                           // [Cout][3][3][3] (kh,kw,c) fp32
+  const float* bias; int cout; int leaky;
+  void* out; int out_pitch; int Cp; int is_fp16;
+};
+int launch_first_conv(const FirstConvParams& p, cudaStream_t s);
+int launch_s2_gather(const void* in, int in_pitch, int C8, int batch, int H, int W,
+                     void* planes, long long plane_rows, cudaStream_t s);
+int launch_upsample2(const void* in, int in_pitch, int Cp, int batch, int H, int W,
+                     void* out, int out_pitch, cudaStream_t s);
+int launch_maxpool(const void* in, int in_pitch, int Cp, int batch, int H, int W, int size, int stride,
+                   void* out, int out_pitch, int is_fp16, cudaStream_t s);
+int launch_add(const void* a, int a_pitch, const void* b, int b_pitch, int Cp, long long rows,
+               void* out, int out_pitch, int is_fp16, cudaStream_t s);
+int launch_copy_channels(const void* in, int in_pitch, int Cp, long long rows, void* out, int out_pitch,
+                         cudaStream_t s);
+int launch_dump_nchw(const void* in, int in_pitch, int C, int batch, int H, int W, int is_fp16,
+                     float* out, cudaStream_t s);
+struct RefConvParams {
+  const void* in; int in_pitch; int Cin_p; int H, W;          // input (unpadded H,W)
+  const void* w; int ktot;                                     // [Cout_p][taps*Cin_p] 16-bit
+  const float* bias; int cout_p; int size, stride; int leaky;
+  const void* residual; int res_pitch;
+  void* out; int out_pitch; int Ho, Wo; int batch; int is_fp16;
+  float* raw_f32;                                              // head: [P_out][cout_p] fp32 instead of `out`
+};
+int launch_ref_conv(const RefConvParams& p, cudaStream_t s);
+struct DecodeParams {
+  const float* raw; int raw_pitch; int batch; int G; int n_anchors; int dec_cols;
+  float stride; float anchor_w[8], anchor_h[8];
+  float* dec_out; int dec_rows_total, dec_row_off;
+};
+int launch_decode(const DecodeParams& p, cudaStream_t s);
+
+// nms.cu / merge.cu -----------------------------------------------------------
+struct NmsScratch {
+  void* buf = nullptr; size_t bytes = 0;
+};
+size_t nms_scratch_bytes(int batch, int n_rows);
+int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres,
+               float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap,
+               void* scratch, size_t scratch_bytes, unsigned int* err_flag, cudaStream_t s);
+size_t merge_scratch_bytes(int batch, int cap);
+int launch_rescale_merge(const float* rows, const int32_t* counts, int batch, int cap,
+                         float pad_x_half, float pad_y_half, float unpad_w, float unpad_h,
+                         float orig_w, float orig_h, int merge,
+                         float* out_rows, int32_t* out_counts, void* scratch, size_t scratch_bytes,
+                         unsigned int* err_flag, cudaStream_t s);
+int launch_bbox_iou(const float* b1, int n1, const float* b2, int n2, float* out, cudaStream_t s);
+
+}  // namespace ay

@@ -1,0 +1,784 @@
+// Host side of the engine: network plan, buffers, tensor maps, per-layer launches
+// and the extern "C" boundary declared in include/amyloid_yolo.h.
+//
+// Plan = the reference's Darknet.forward layer loop (models.py:237-255) resolved at
+// build time: every cfg block gets an output "view" (zero-haloed NHWC rows, see
+// ay_common.h); shortcuts are folded into the producing convolution's epilogue,
+// single-source routes alias their source, multi-source routes become a shared
+// concat buffer that the producers write into directly, [yolo] blocks become the
+// decode epilogue of the preceding head convolution.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "ay_common.h"
+
+namespace ay {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// 2-D K-major map over `rows` rows of `inner` 16-bit elements, row pitch `pitch` elements.
+int make_map_2d(CUtensorMap* map, void* base, int inner, long long rows, int pitch, int box_inner, int box_rows,
+                int is_fp16) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return AY_ECUDA;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapSwizzle sw = (box_inner * 2 == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  CUresult r = enc(map, is_fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): inner=%d rows=%lld pitch=%d box=%dx%d base=%p", (int)r, inner, rows,
+              pitch, box_inner, box_rows, base);
+    return AY_ECUDA;
+  }
+  return AY_OK;
+}
+
+uint16_t to16(float v, int is_fp16) {
+  if (is_fp16) {
+    __half h = __float2half_rn(v);
+    uint16_t u;
+    memcpy(&u, &h, 2);
+    return u;
+  }
+  __nv_bfloat16 b = __float2bfloat16_rn(v);
+  uint16_t u;
+  memcpy(&u, &b, 2);
+  return u;
+}
+
+struct Layer {
+  ay_layer_desc d;
+  int C = 0, H = 0, W = 0;          // logical output shape
+  ActView out;                      // where the output lives (ptr == nullptr: not materialised)
+  bool owns = false;                // this layer allocated out.ptr
+  // convolution
+  int cin = 0, cin_p = 0, cout_rows = 0, ktot = 0, BN = 0, BK = 0, stages = 0;
+  int impl = 0;                     // 0 none, 1 tcgen05 gemm, 2 first-layer direct
+  void* w16 = nullptr;              // [cout_rows][ktot] 16-bit (gemm)
+  float* w32 = nullptr;             // [cout][27] fp32 (first layer)
+  float* bias = nullptr;            // [cout_rows]
+  bool weights_set = false;
+  int fused_shortcut = -1;          // index of the [shortcut] folded into this conv's epilogue
+  int residual_src = -1;
+  bool is_head = false;             // followed by [yolo]: decode fused
+  int yolo_layer = -1;
+  void* planes = nullptr;           // stride-2: parity planes [4][plane_rows][cin_p]
+  long long plane_rows = 0;
+  float* raw_f32 = nullptr;         // reference path scratch for heads
+  CUtensorMap tmA, tmB;
+  // yolo
+  int dec_row_off = 0;
+  // route copy fallback
+  std::vector<int> copy_srcs;       // sources that must be copied into the concat buffer
+  std::vector<int> copy_offs;
+  bool fused_into_prev = false;     // shortcut handled by the previous conv
+};
+
+}  // namespace
+}  // namespace ay
+
+struct ay_ctx {
+  int device = 0;
+  int num_sms = 148;
+  unsigned int* err_flag = nullptr;   // device
+  // network
+  std::vector<ay::Layer> layers;
+  int in_channels = 3, img_size = 416, max_batch = 0, is_fp16 = 0;
+  bool built = false, finalized = false, use_ref = false;
+  int dec_rows = 0, dec_cols = 0;
+  int* idx_y = nullptr;               // nearest-resize tables (device), rebuilt when the source size changes
+  int* idx_x = nullptr;
+  int idx_src_h = -1, idx_src_w = -1;
+  std::vector<void*> allocs;
+  int launches = 0;
+  // post-processing scratch
+  void* nms_scratch = nullptr; size_t nms_bytes = 0;
+  void* merge_scratch = nullptr; size_t merge_bytes = 0;
+};
+
+namespace ay {
+namespace {
+
+int dev_alloc(ay_ctx* ctx, void** p, size_t bytes, bool zero) {
+  if (bytes == 0) bytes = 256;
+  cudaError_t e = cudaMalloc(p, bytes);
+  if (e != cudaSuccess) {
+    set_error("cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+    return AY_ENOMEM;
+  }
+  ctx->allocs.push_back(*p);
+  if (zero) AY_CUDA(cudaMemset(*p, 0, bytes));
+  return AY_OK;
+}
+
+void free_network(ay_ctx* ctx) {
+  for (void* p : ctx->allocs) cudaFree(p);
+  ctx->allocs.clear();
+  ctx->layers.clear();
+  ctx->built = ctx->finalized = false;
+  ctx->idx_y = ctx->idx_x = nullptr;
+  ctx->idx_src_h = ctx->idx_src_w = -1;
+}
+
+long long padded_rows(int batch, int H, int W) { return (long long)batch * (H + 2) * (W + 2); }
+
+int alloc_view(ay_ctx* ctx, ActView* v, int C, int H, int W) {
+  v->C = C;
+  v->Cp = round_up(C, 32);
+  v->H = H;
+  v->W = W;
+  v->pitch = v->Cp;
+  v->rows_alloc = padded_rows(ctx->max_batch, H, W);
+  // zero-filled so that channel padding and never-written rows hold finite zeros
+  return dev_alloc(ctx, &v->ptr, (size_t)v->rows_alloc * v->pitch * 2, true);
+}
+
+}  // namespace
+}  // namespace ay
+
+// =============================================================================
+// C ABI
+// =============================================================================
+using ay::Layer;
+using ay::ActView;
+using ay::set_error;
+
+#define AY_ENTER(ctx)                                   \
+  do {                                                  \
+    if (!(ctx)) {                                       \
+      set_error("null context");                        \
+      return AY_EINVAL;                                 \
+    }                                                   \
+    AY_CUDA(cudaSetDevice((ctx)->device));              \
+  } while (0)
+
+#define AY_TRY(expr)               \
+  do {                             \
+    int _r = (expr);               \
+    if (_r != AY_OK) return _r;    \
+  } while (0)
+
+extern "C" const char* ay_last_error(void) { return ay::g_err; }
+extern "C" int ay_abi_version(void) { return 1; }
+
+extern "C" int ay_create(ay_ctx** out, int device) {
+  if (!out) { set_error("ay_create: null output pointer"); return AY_EINVAL; }
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count <= 0) {
+    set_error("no CUDA device available (%s); this engine has no CPU fallback",
+              e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return AY_ECUDA;
+  }
+  if (device < 0 || device >= count) { set_error("device %d out of range (have %d)", device, count); return AY_EINVAL; }
+  AY_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  AY_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
+    return AY_EINVAL;
+  }
+  ay_ctx* ctx = new ay_ctx();
+  ctx->device = device;
+  ctx->num_sms = prop.multiProcessorCount;
+  if (cudaMalloc(&ctx->err_flag, sizeof(unsigned int)) != cudaSuccess) {
+    delete ctx;
+    set_error("cudaMalloc failed");
+    return AY_ENOMEM;
+  }
+  cudaMemset(ctx->err_flag, 0, sizeof(unsigned int));
+  *out = ctx;
+  return AY_OK;
+}
+
+extern "C" int ay_destroy(ay_ctx* ctx) {
+  if (!ctx) return AY_OK;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  ay::free_network(ctx);
+  if (ctx->nms_scratch) cudaFree(ctx->nms_scratch);
+  if (ctx->merge_scratch) cudaFree(ctx->merge_scratch);
+  if (ctx->err_flag) cudaFree(ctx->err_flag);
+  delete ctx;
+  return AY_OK;
+}
+
+extern "C" int ay_check(ay_ctx* ctx, void* stream) {
+  AY_ENTER(ctx);
+  cudaError_t e = cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) { set_error("asynchronous CUDA failure: %s", cudaGetErrorString(e)); return AY_ECUDA; }
+  unsigned int flag = 0;
+  AY_CUDA(cudaMemcpy(&flag, ctx->err_flag, sizeof(flag), cudaMemcpyDeviceToHost));
+  if (flag) {
+    AY_CUDA(cudaMemset(ctx->err_flag, 0, sizeof(flag)));
+    if ((flag & 0xFFFF0000u) == 0xCA9A0000u) {
+      set_error("per-tile capacity exceeded in %s", (flag & 0xFFFF) == 1 ? "nms (more kept boxes than cap)"
+                                                    : (flag & 0xFFFF) == 2 ? "merge (more than 512 detections in a tile)"
+                                                                           : "merge (entry pool)");
+      return AY_ECAPACITY;
+    }
+    set_error("device-side failure flag 0x%08x (pipeline barrier timeout)", flag);
+    return AY_ECUDA;
+  }
+  return AY_OK;
+}
+
+extern "C" int ay_net_use_reference_conv(ay_ctx* ctx, int enable) {
+  if (!ctx) { set_error("null context"); return AY_EINVAL; }
+  ctx->use_ref = enable != 0;
+  return AY_OK;
+}
+
+extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layers, int in_channels, int img_size,
+                            int max_batch, int act_dtype) {
+  AY_ENTER(ctx);
+  if (!descs || n_layers <= 0 || max_batch <= 0 || img_size <= 0 || img_size % 32 != 0 ||
+      (act_dtype != AY_BF16 && act_dtype != AY_FP16)) {
+    set_error("ay_net_build: bad arguments (n_layers=%d max_batch=%d img_size=%d dtype=%d)", n_layers, max_batch,
+              img_size, act_dtype);
+    return AY_EINVAL;
+  }
+  AY_CUDA(cudaDeviceSynchronize());
+  ay::free_network(ctx);
+  ctx->in_channels = in_channels;
+  ctx->img_size = img_size;
+  ctx->max_batch = max_batch;
+  ctx->is_fp16 = act_dtype == AY_FP16;
+  ctx->layers.resize(n_layers);
+  std::vector<Layer>& Ls = ctx->layers;
+
+  // ---- pass 1: shapes (models.py:16-83 bookkeeping of output_filters, plus spatial sizes)
+  int pc = in_channels, ph = img_size, pw = img_size;
+  std::vector<std::vector<int>> explicit_refs(n_layers);
+  ctx->dec_rows = 0;
+  ctx->dec_cols = 0;
+  for (int i = 0; i < n_layers; ++i) {
+    Layer& L = Ls[i];
+    L.d = descs[i];
+    const ay_layer_desc& d = L.d;
+    switch (d.type) {
+      case AY_CONV: {
+        if (d.size != 1 && d.size != 3) { set_error("layer %d: conv size %d unsupported", i, d.size); return AY_EINVAL; }
+        if (d.stride != 1 && d.stride != 2) { set_error("layer %d: conv stride %d unsupported", i, d.stride); return AY_EINVAL; }
+        const int pad = (d.size - 1) / 2;
+        L.cin = pc;
+        L.C = d.filters;
+        L.H = (ph + 2 * pad - d.size) / d.stride + 1;
+        L.W = (pw + 2 * pad - d.size) / d.stride + 1;
+        break;
+      }
+      case AY_MAXPOOL:
+        L.C = pc;
+        L.H = d.stride == 2 ? ph / 2 : ph;
+        L.W = d.stride == 2 ? pw / 2 : pw;
+        break;
+      case AY_UPSAMPLE:
+        if (d.stride != 2) { set_error("layer %d: upsample stride %d unsupported", i, d.stride); return AY_EINVAL; }
+        L.C = pc; L.H = ph * 2; L.W = pw * 2;
+        break;
+      case AY_ROUTE: {
+        if (d.n_src < 1 || d.n_src > 4) { set_error("layer %d: route with %d sources", i, d.n_src); return AY_EINVAL; }
+        int c = 0;
+        for (int k = 0; k < d.n_src; ++k) {
+          const int s = d.src[k];
+          if (s < 0 || s >= i) { set_error("layer %d: route source %d out of range", i, s); return AY_EINVAL; }
+          if (k && (Ls[s].H != Ls[d.src[0]].H || Ls[s].W != Ls[d.src[0]].W)) {
+            set_error("layer %d: route sources differ in size", i); return AY_EINVAL;
+          }
+          c += Ls[s].C;
+          explicit_refs[s].push_back(i);
+        }
+        L.C = c; L.H = Ls[d.src[0]].H; L.W = Ls[d.src[0]].W;
+        break;
+      }
+      case AY_SHORTCUT: {
+        const int s = d.src[0];
+        if (i == 0 || s < 0 || s >= i || Ls[s].C != pc || Ls[s].H != ph || Ls[s].W != pw) {
+          set_error("layer %d: shortcut source %d has a different shape", i, s); return AY_EINVAL;
+        }
+        explicit_refs[s].push_back(i);
+        L.C = pc; L.H = ph; L.W = pw;
+        break;
+      }
+      case AY_YOLO: {
+        if (i == 0 || Ls[i - 1].d.type != AY_CONV || d.n_anchors < 1 || d.n_anchors > 8 ||
+            pc != d.n_anchors * (5 + d.classes) || ph != pw) {
+          set_error("layer %d: yolo block must follow a conv with %d*(5+%d) filters", i, d.n_anchors, d.classes);
+          return AY_EINVAL;
+        }
+        if (ctx->dec_cols && ctx->dec_cols != 5 + d.classes) { set_error("yolo blocks disagree on classes"); return AY_EINVAL; }
+        ctx->dec_cols = 5 + d.classes;
+        L.dec_row_off = ctx->dec_rows;
+        ctx->dec_rows += d.n_anchors * ph * pw;
+        L.C = pc; L.H = ph; L.W = pw;
+        break;
+      }
+      default:
+        set_error("layer %d: unknown type %d", i, d.type);
+        return AY_EINVAL;
+    }
+    pc = L.C; ph = L.H; pw = L.W;
+  }
+  if (ctx->dec_rows == 0) { set_error("network has no [yolo] block"); return AY_EINVAL; }
+
+  // ---- pass 2: fusion decisions
+  for (int i = 0; i < n_layers; ++i) {
+    Layer& L = Ls[i];
+    if (L.d.type == AY_CONV) {
+      const bool first = (i == 0 && L.cin == in_channels && L.cin < 8);
+      if (first) {
+        if (L.d.size != 3 || L.d.stride != 1 || in_channels != 3) {
+          set_error("first convolution must be 3x3 stride 1 over 3 channels"); return AY_EINVAL;
+        }
+        L.impl = 2;
+      } else {
+        L.impl = 1;
+        if (L.d.stride == 2 && (L.d.size != 3 || (Ls[i - 1].H & 1) || (Ls[i - 1].W & 1))) {
+          set_error("layer %d: stride-2 conv needs size 3 and even input", i); return AY_EINVAL;
+        }
+      }
+      if (i + 1 < n_layers && Ls[i + 1].d.type == AY_YOLO) {
+        if (L.impl != 1 || !explicit_refs[i].empty()) { set_error("layer %d: unsupported head layout", i); return AY_EINVAL; }
+        L.is_head = true;
+        L.yolo_layer = i + 1;
+      } else if (i + 1 < n_layers && Ls[i + 1].d.type == AY_SHORTCUT && L.impl == 1 && explicit_refs[i].empty()) {
+        L.fused_shortcut = i + 1;
+        L.residual_src = Ls[i + 1].d.src[0];
+        Ls[i + 1].fused_into_prev = true;
+      }
+    }
+  }
+
+  // ---- pass 3a: multi-source routes own a concat buffer; sources write into it when possible
+  std::vector<char> placed(n_layers, 0);
+  for (int i = 0; i < n_layers; ++i) {
+    Layer& L = Ls[i];
+    if (L.d.type != AY_ROUTE || L.d.n_src < 2) continue;
+    for (int k = 0; k < L.d.n_src; ++k)
+      if (Ls[L.d.src[k]].C % 32 != 0) { set_error("layer %d: concat of a %d-channel tensor unsupported", i, Ls[L.d.src[k]].C); return AY_EINVAL; }
+    AY_TRY(ay::alloc_view(ctx, &L.out, L.C, L.H, L.W));
+    L.owns = true;
+    placed[i] = 1;
+    int off = 0;
+    for (int k = 0; k < L.d.n_src; ++k) {
+      const int s = L.d.src[k];
+      Layer& S = Ls[s];
+      const bool materialises = (S.d.type == AY_CONV && !S.is_head && S.fused_shortcut < 0) || S.d.type == AY_MAXPOOL ||
+                                S.d.type == AY_UPSAMPLE || S.d.type == AY_SHORTCUT;
+      if (materialises && !placed[s]) {
+        S.out = L.out;
+        S.out.ptr = static_cast<uint16_t*>(L.out.ptr) + off;
+        S.out.C = S.C;
+        S.out.Cp = S.C;
+        placed[s] = 1;
+      } else {
+        L.copy_srcs.push_back(s);
+        L.copy_offs.push_back(off);
+      }
+      off += S.C;
+    }
+  }
+  // ---- pass 3b: everything else
+  for (int i = 0; i < n_layers; ++i) {
+    Layer& L = Ls[i];
+    const int t = L.d.type;
+    const bool materialises = (t == AY_CONV && !L.is_head && L.fused_shortcut < 0) || t == AY_MAXPOOL ||
+                              t == AY_UPSAMPLE || t == AY_SHORTCUT;
+    if (materialises && !placed[i]) {
+      AY_TRY(ay::alloc_view(ctx, &L.out, L.C, L.H, L.W));
+      L.owns = true;
+      placed[i] = 1;
+    } else if (t == AY_ROUTE && L.d.n_src == 1) {
+      L.out = Ls[L.d.src[0]].out;
+      if (!L.out.ptr) { set_error("layer %d: route source %d is not materialised", i, L.d.src[0]); return AY_EINVAL; }
+    }
+  }
+
+  // ---- pass 4: convolution resources
+  for (int i = 0; i < n_layers; ++i) {
+    Layer& L = Ls[i];
+    if (L.d.type != AY_CONV) continue;
+    if (L.impl == 2) {
+      AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.w32), sizeof(float) * L.C * 27, true));
+      AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.C, true));
+      continue;
+    }
+    const ActView& in = Ls[i - 1].out;
+    if (!in.ptr) { set_error("layer %d: input of the convolution is not materialised", i); return AY_EINVAL; }
+    const int taps = L.d.size * L.d.size;
+    L.cin_p = in.Cp;
+    L.ktot = taps * L.cin_p;
+    L.BK = (L.cin_p % 64 == 0) ? 64 : 32;
+    const int cout_p = ay::round_up(L.C, 32);
+    if (L.is_head) L.BN = cout_p <= 256 ? cout_p : 256;
+    else L.BN = (cout_p % 256 == 0) ? 256 : (cout_p % 128 == 0) ? 128 : (cout_p % 64 == 0) ? 64 : 32;
+    L.cout_rows = ay::round_up(cout_p, L.BN);
+    L.stages = ay::conv_gemm_pick_stages(L.BN, L.BK);
+    AY_TRY(ay::dev_alloc(ctx, &L.w16, (size_t)L.cout_rows * L.ktot * 2, true));
+    AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.cout_rows, true));
+    AY_TRY(ay::make_map_2d(&L.tmB, L.w16, L.ktot, L.cout_rows, L.ktot, L.BK, L.BN, ctx->is_fp16));
+    if (L.d.stride == 2) {
+      L.plane_rows = ay::padded_rows(max_batch, L.H, L.W);
+      AY_TRY(ay::dev_alloc(ctx, &L.planes, (size_t)4 * L.plane_rows * L.cin_p * 2, true));
+      AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, L.BK, 128, ctx->is_fp16));
+    } else {
+      AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, L.BK, 128, ctx->is_fp16));
+    }
+    if (L.is_head)
+      AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.raw_f32),
+                           sizeof(float) * (size_t)ay::padded_rows(max_batch, L.H, L.W) * L.cout_rows, true));
+  }
+  AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_y), sizeof(int) * img_size, true));
+  AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_x), sizeof(int) * img_size, true));
+  AY_CUDA(cudaDeviceSynchronize());
+  ctx->built = true;
+  return AY_OK;
+}
+
+extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const float* bias) {
+  AY_ENTER(ctx);
+  if (!ctx->built || layer < 0 || layer >= (int)ctx->layers.size() || ctx->layers[layer].d.type != AY_CONV || !w || !bias) {
+    set_error("ay_net_set_conv: bad layer %d", layer);
+    return AY_EINVAL;
+  }
+  Layer& L = ctx->layers[layer];
+  const int k = L.d.size, taps = k * k, cout = L.C, cin = L.cin;
+  if (L.impl == 2) {
+    std::vector<float> r((size_t)cout * 27);
+    for (int o = 0; o < cout; ++o)
+      for (int c = 0; c < 3; ++c)
+        for (int t = 0; t < 9; ++t) r[(size_t)o * 27 + t * 3 + c] = w[((size_t)o * 3 + c) * 9 + t];
+    AY_CUDA(cudaMemcpy(L.w32, r.data(), r.size() * sizeof(float), cudaMemcpyHostToDevice));
+    AY_CUDA(cudaMemcpy(L.bias, bias, sizeof(float) * cout, cudaMemcpyHostToDevice));
+  } else {
+    std::vector<uint16_t> r((size_t)L.cout_rows * L.ktot, 0);
+    for (int o = 0; o < cout; ++o)
+      for (int c = 0; c < cin; ++c)
+        for (int t = 0; t < taps; ++t)
+          r[(size_t)o * L.ktot + (size_t)t * L.cin_p + c] = ay::to16(w[((size_t)o * cin + c) * taps + t], ctx->is_fp16);
+    std::vector<float> b(L.cout_rows, 0.f);
+    memcpy(b.data(), bias, sizeof(float) * cout);
+    AY_CUDA(cudaMemcpy(L.w16, r.data(), r.size() * 2, cudaMemcpyHostToDevice));
+    AY_CUDA(cudaMemcpy(L.bias, b.data(), sizeof(float) * L.cout_rows, cudaMemcpyHostToDevice));
+  }
+  L.weights_set = true;
+  ctx->finalized = false;
+  return AY_OK;
+}
+
+extern "C" int ay_net_finalize(ay_ctx* ctx) {
+  AY_ENTER(ctx);
+  if (!ctx->built) { set_error("ay_net_finalize before ay_net_build"); return AY_ESTATE; }
+  for (size_t i = 0; i < ctx->layers.size(); ++i)
+    if (ctx->layers[i].d.type == AY_CONV && !ctx->layers[i].weights_set) {
+      set_error("layer %zu has no weights", i);
+      return AY_ESTATE;
+    }
+  ctx->finalized = true;
+  return AY_OK;
+}
+
+extern "C" int ay_net_output_shape(ay_ctx* ctx, int* rows, int* cols) {
+  if (!ctx || !ctx->built) { set_error("network not built"); return AY_ESTATE; }
+  if (rows) *rows = ctx->dec_rows;
+  if (cols) *cols = ctx->dec_cols;
+  return AY_OK;
+}
+
+extern "C" int ay_net_layer_shape(ay_ctx* ctx, int layer, int* c, int* h, int* w) {
+  if (!ctx || !ctx->built || layer < 0 || layer >= (int)ctx->layers.size()) { set_error("bad layer"); return AY_EINVAL; }
+  if (c) *c = ctx->layers[layer].C;
+  if (h) *h = ctx->layers[layer].H;
+  if (w) *w = ctx->layers[layer].W;
+  return AY_OK;
+}
+
+extern "C" int ay_net_layer_impl(ay_ctx* ctx, int layer) {
+  if (!ctx || !ctx->built || layer < 0 || layer >= (int)ctx->layers.size()) return 0;
+  const Layer& L = ctx->layers[layer];
+  if (L.d.type != AY_CONV) return 0;
+  return (L.impl == 1 && ctx->use_ref) ? 3 : L.impl;
+}
+
+extern "C" int ay_net_launch_count(ay_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+namespace {
+
+// ATen's nearest-neighbour source index (UpSample.h nearest_neighbor_compute_source_index):
+// min(floor(dst * float(src)/float(dst)), src-1), all in fp32.
+void nearest_table(int dst, int src, std::vector<int>* out) {
+  out->resize(dst);
+  const float scale = (float)src / (float)dst;
+  for (int i = 0; i < dst; ++i) {
+    int s = (int)floorf((float)i * scale);
+    (*out)[i] = s < src - 1 ? s : src - 1;
+  }
+}
+
+int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int src_h, int src_w, float* dec_out,
+             cudaStream_t st) {
+  std::vector<Layer>& Ls = ctx->layers;
+  Layer& L = Ls[i];
+  const ActView* target = L.fused_shortcut >= 0 ? &Ls[L.fused_shortcut].out : &L.out;
+  if (L.impl == 2) {
+    ay::FirstConvParams p{};
+    p.in = input; p.in_kind = in_kind; p.batch = batch; p.S = ctx->img_size; p.src_h = src_h; p.src_w = src_w;
+    p.idx_y = ctx->idx_y; p.idx_x = ctx->idx_x; p.w = L.w32; p.bias = L.bias; p.cout = L.C; p.leaky = L.d.leaky;
+    p.out = target->ptr; p.out_pitch = target->pitch; p.Cp = target->Cp; p.is_fp16 = ctx->is_fp16;
+    ++ctx->launches;
+    return ay::launch_first_conv(p, st);
+  }
+  const ActView& in = Ls[i - 1].out;
+  const int Hq = L.H + 2, Wq = L.W + 2;
+  const ActView* res = L.residual_src >= 0 ? &Ls[L.residual_src].out : nullptr;
+  const Layer* Y = L.is_head ? &Ls[L.yolo_layer] : nullptr;
+
+  if (ctx->use_ref) {
+    ay::RefConvParams r{};
+    r.in = in.ptr; r.in_pitch = in.pitch; r.Cin_p = L.cin_p; r.H = in.H; r.W = in.W;
+    r.w = L.w16; r.ktot = L.ktot; r.bias = L.bias; r.cout_p = L.is_head ? L.cout_rows : target->Cp;
+    r.size = L.d.size; r.stride = L.d.stride; r.leaky = L.d.leaky;
+    r.residual = res ? res->ptr : nullptr; r.res_pitch = res ? res->pitch : 0;
+    r.out = L.is_head ? nullptr : target->ptr; r.out_pitch = L.is_head ? 0 : target->pitch;
+    r.Ho = L.H; r.Wo = L.W; r.batch = batch; r.is_fp16 = ctx->is_fp16;
+    r.raw_f32 = L.is_head ? L.raw_f32 : nullptr;
+    ++ctx->launches;
+    AY_TRY(ay::launch_ref_conv(r, st));
+    if (L.is_head) {
+      ay::DecodeParams d{};
+      d.raw = L.raw_f32; d.raw_pitch = L.cout_rows; d.batch = batch; d.G = L.H; d.n_anchors = Y->d.n_anchors;
+      d.dec_cols = ctx->dec_cols; d.stride = (float)((double)ctx->img_size / (double)L.H);
+      for (int a = 0; a < Y->d.n_anchors; ++a) {
+        d.anchor_w[a] = (float)((double)Y->d.anchors[2 * a] / ((double)ctx->img_size / (double)L.H));
+        d.anchor_h[a] = (float)((double)Y->d.anchors[2 * a + 1] / ((double)ctx->img_size / (double)L.H));
+      }
+      d.dec_out = dec_out; d.dec_rows_total = ctx->dec_rows; d.dec_row_off = Y->dec_row_off;
+      ++ctx->launches;
+      AY_TRY(ay::launch_decode(d, st));
+    }
+    return AY_OK;
+  }
+
+  ay::ConvGemmParams p{};
+  p.P = (int)ay::padded_rows(batch, L.H, L.W);
+  p.num_m_tiles = (p.P + 127) / 128;
+  p.num_n_tiles = L.cout_rows / L.BN;
+  p.n_taps = L.d.size * L.d.size;
+  p.kb_per_tap = L.cin_p / L.BK;
+  if (L.d.size == 1) {
+    p.a_row_off[0] = 0;
+  } else if (L.d.stride == 1) {
+    for (int kh = 0; kh < 3; ++kh)
+      for (int kw = 0; kw < 3; ++kw) p.a_row_off[kh * 3 + kw] = (kh - 1) * Wq + (kw - 1);
+  } else {
+    AY_TRY(ay::launch_s2_gather(in.ptr, in.pitch, L.cin_p / 8, batch, in.H, in.W, L.planes, L.plane_rows, st));
+    ++ctx->launches;
+    for (int kh = 0; kh < 3; ++kh)
+      for (int kw = 0; kw < 3; ++kw) {
+        const long long off = (long long)((kh & 1) * 2 + (kw & 1)) * L.plane_rows + (kh >> 1) * Wq + (kw >> 1);
+        if (off > 0x7fffffffLL - (1LL << 26)) { set_error("layer %d: batch too large for 32-bit row offsets", i); return AY_EINVAL; }
+        p.a_row_off[kh * 3 + kw] = (int)off;
+      }
+  }
+  p.BN = L.BN; p.BK = L.BK; p.num_stages = L.stages;
+  p.Hp = Hq; p.Wp = Wq;
+  p.bias = L.bias; p.leaky = L.d.leaky; p.is_fp16 = ctx->is_fp16;
+  p.err_flag = ctx->err_flag;
+  if (L.is_head) {
+    p.head = 1;
+    p.dec_out = dec_out; p.dec_rows_total = ctx->dec_rows; p.dec_row_off = Y->dec_row_off;
+    p.dec_cols = ctx->dec_cols; p.n_anchors = Y->d.n_anchors; p.cout = L.C;
+    const double stride = (double)ctx->img_size / (double)L.H;   // models.py:119
+    p.stride = (float)stride;
+    for (int a = 0; a < Y->d.n_anchors; ++a) {
+      p.anchor_w[a] = (float)((double)Y->d.anchors[2 * a] / stride);      // models.py:122-124
+      p.anchor_h[a] = (float)((double)Y->d.anchors[2 * a + 1] / stride);
+    }
+  } else {
+    p.out = target->ptr; p.out_pitch = target->pitch;
+    p.residual = res ? res->ptr : nullptr; p.res_pitch = res ? res->pitch : 0;
+    p.cout = L.C;
+  }
+  ++ctx->launches;
+  return ay::launch_conv_gemm(L.tmA, L.tmB, p, ctx->num_sms, st);
+}
+
+}  // namespace
+
+extern "C" int ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                          float* out_decoded, void* stream) {
+  AY_ENTER(ctx);
+  if (!ctx->finalized) { set_error("ay_forward before ay_net_finalize"); return AY_ESTATE; }
+  if (!input || !out_decoded || batch < 1 || batch > ctx->max_batch) {
+    set_error("ay_forward: bad arguments (batch=%d, capacity %d)", batch, ctx->max_batch);
+    return AY_EINVAL;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (in_kind == AY_IN_F32_NCHW) {
+    if (src_h != ctx->img_size || src_w != ctx->img_size) {
+      set_error("ay_forward: float input must be %dx%d (got %dx%d)", ctx->img_size, ctx->img_size, src_h, src_w);
+      return AY_EINVAL;
+    }
+  } else if (in_kind == AY_IN_U8_HWC) {
+    if (src_h != src_w || src_h < 1) { set_error("ay_forward: uint8 tiles must be square (got %dx%d)", src_h, src_w); return AY_EINVAL; }
+    if (src_h != ctx->idx_src_h || src_w != ctx->idx_src_w) {
+      std::vector<int> ty, tx;
+      nearest_table(ctx->img_size, src_h, &ty);
+      nearest_table(ctx->img_size, src_w, &tx);
+      AY_CUDA(cudaStreamSynchronize(st));
+      AY_CUDA(cudaMemcpy(ctx->idx_y, ty.data(), sizeof(int) * ty.size(), cudaMemcpyHostToDevice));
+      AY_CUDA(cudaMemcpy(ctx->idx_x, tx.data(), sizeof(int) * tx.size(), cudaMemcpyHostToDevice));
+      ctx->idx_src_h = src_h;
+      ctx->idx_src_w = src_w;
+    }
+  } else {
+    set_error("ay_forward: unknown input kind %d", in_kind);
+    return AY_EINVAL;
+  }
+  ctx->launches = 0;
+  std::vector<Layer>& Ls = ctx->layers;
+  for (int i = 0; i < (int)Ls.size(); ++i) {
+    Layer& L = Ls[i];
+    switch (L.d.type) {
+      case AY_CONV:
+        AY_TRY(run_conv(ctx, i, input, in_kind, batch, src_h, src_w, out_decoded, st));
+        break;
+      case AY_MAXPOOL: {
+        const ActView& in = Ls[i - 1].out;
+        AY_TRY(ay::launch_maxpool(in.ptr, in.pitch, in.Cp, batch, in.H, in.W, L.d.size, L.d.stride, L.out.ptr,
+                                  L.out.pitch, ctx->is_fp16, st));
+        ++ctx->launches;
+        break;
+      }
+      case AY_UPSAMPLE: {
+        const ActView& in = Ls[i - 1].out;
+        AY_TRY(ay::launch_upsample2(in.ptr, in.pitch, in.Cp, batch, in.H, in.W, L.out.ptr, L.out.pitch, st));
+        ++ctx->launches;
+        break;
+      }
+      case AY_ROUTE:
+        for (size_t k = 0; k < L.copy_srcs.size(); ++k) {
+          const ActView& s = Ls[L.copy_srcs[k]].out;
+          AY_TRY(ay::launch_copy_channels(s.ptr, s.pitch, s.Cp, ay::padded_rows(batch, s.H, s.W),
+                                          static_cast<uint16_t*>(L.out.ptr) + L.copy_offs[k], L.out.pitch, st));
+          ++ctx->launches;
+        }
+        break;
+      case AY_SHORTCUT:
+        if (!L.fused_into_prev) {
+          const ActView& a = Ls[i - 1].out;
+          const ActView& b = Ls[L.d.src[0]].out;
+          AY_TRY(ay::launch_add(a.ptr, a.pitch, b.ptr, b.pitch, L.out.Cp, ay::padded_rows(batch, L.H, L.W), L.out.ptr,
+                                L.out.pitch, ctx->is_fp16, st));
+          ++ctx->launches;
+        }
+        break;
+      default:
+        break;
+    }
+  }
+  return AY_OK;
+}
+
+extern "C" int ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out_nchw, void* stream) {
+  AY_ENTER(ctx);
+  if (!ctx->built || layer < 0 || layer >= (int)ctx->layers.size() || batch < 1 || batch > ctx->max_batch) {
+    set_error("ay_net_layer_output: bad arguments");
+    return AY_EINVAL;
+  }
+  const Layer& L = ctx->layers[layer];
+  if (!L.out.ptr) { set_error("layer %d is fused into its consumer and has no stored output", layer); return AY_EINVAL; }
+  return ay::launch_dump_nchw(L.out.ptr, L.out.pitch, L.C, batch, L.H, L.W, ctx->is_fp16, out_nchw,
+                              static_cast<cudaStream_t>(stream));
+}
+
+static int ensure_scratch(void** buf, size_t* have, size_t need) {
+  if (*have >= need) return AY_OK;
+  AY_CUDA(cudaDeviceSynchronize());
+  if (*buf) cudaFree(*buf);
+  *buf = nullptr;
+  *have = 0;
+  cudaError_t e = cudaMalloc(buf, need);
+  if (e != cudaSuccess) { set_error("cudaMalloc(%zu bytes of scratch) failed: %s", need, cudaGetErrorString(e)); return AY_ENOMEM; }
+  *have = need;
+  return AY_OK;
+}
+
+extern "C" int ay_nms(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes, float conf_thres,
+                      float nms_thres, float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream) {
+  AY_ENTER(ctx);
+  if (!pred || !out_rows || !out_keep || !out_counts || batch < 1 || n_rows < 1) {
+    set_error("ay_nms: bad arguments");
+    return AY_EINVAL;
+  }
+  AY_TRY(ensure_scratch(&ctx->nms_scratch, &ctx->nms_bytes, ay::nms_scratch_bytes(batch, n_rows)));
+  return ay::launch_nms(pred, batch, n_rows, n_classes, conf_thres, nms_thres, out_rows, out_keep, out_counts, cap,
+                        ctx->nms_scratch, ctx->nms_bytes, ctx->err_flag, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* counts, int batch, int cap,
+                                int current_dim, int orig_h, int orig_w, int merge, float* out_rows,
+                                int32_t* out_counts, void* stream) {
+  AY_ENTER(ctx);
+  if (!rows || !counts || !out_rows || !out_counts || batch < 1 || cap < 1 || current_dim < 1 || orig_h < 1 || orig_w < 1) {
+    set_error("ay_rescale_merge: bad arguments");
+    return AY_EINVAL;
+  }
+  AY_TRY(ensure_scratch(&ctx->merge_scratch, &ctx->merge_bytes, ay::merge_scratch_bytes(batch, cap)));
+  // utils/utils.py:38-45 in double (python floats), rounded to fp32 where they meet the tensor
+  const double mx = (double)std::max(orig_h, orig_w);
+  const double pad_x = (double)std::max(orig_h - orig_w, 0) * ((double)current_dim / mx);
+  const double pad_y = (double)std::max(orig_w - orig_h, 0) * ((double)current_dim / mx);
+  const double unpad_h = (double)current_dim - pad_y, unpad_w = (double)current_dim - pad_x;
+  return ay::launch_rescale_merge(rows, counts, batch, cap, (float)floor(pad_x / 2.0), (float)floor(pad_y / 2.0),
+                                  (float)unpad_w, (float)unpad_h, (float)orig_w, (float)orig_h, merge, out_rows,
+                                  out_counts, ctx->merge_scratch, ctx->merge_bytes, ctx->err_flag,
+                                  static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ay_bbox_iou(ay_ctx* ctx, const float* box1, int n1, const float* box2, int n2, float* out_iou,
+                           void* stream) {
+  AY_ENTER(ctx);
+  if (!box1 || !box2 || !out_iou || (n1 != 1 && n1 != n2)) { set_error("ay_bbox_iou: bad arguments"); return AY_EINVAL; }
+  return ay::launch_bbox_iou(box1, n1, box2, n2, out_iou, static_cast<cudaStream_t>(stream));
+}

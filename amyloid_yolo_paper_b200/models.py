@@ -108,7 +108,8 @@ class Darknet(nn.Module):
         self.header_info = np.array([0, 0, 0, self.seen, 0], dtype=np.int32)
         self._engine = None           # built lazily on first forward (needs a GPU)
         self._engine_key = None
-        self.precision = "bf16"
+        self._weights_epoch = 0
+        self.precision = "bf16"       # activation storage of the tensor-core path: "bf16" | "fp16"
 
     # ------------------------------------------------------------------ engine
     def engine(self, device=None, max_batch=None):
@@ -120,13 +121,13 @@ class Darknet(nn.Module):
             device = p.device if p.is_cuda else torch.device("cuda", torch.cuda.current_device()
                                                              if torch.cuda.is_available() else 0)
         version = tuple(int(p._version) for p in self.state_dict().values())
-        key = (str(device), version)
+        key = (str(device), version, self.precision, self._weights_epoch)
         if self._engine is None or self._engine_key != key or \
                 (max_batch is not None and max_batch > self._engine.max_batch):
             if self._engine is not None:
                 self._engine.close()
             self._engine = Engine(self.module_defs, self.hyperparams, self.state_dict(), device,
-                                  max_batch=max_batch or 8)
+                                  max_batch=max_batch or 8, precision=self.precision)
             self._engine_key = key
         return self._engine
 
@@ -136,7 +137,9 @@ class Darknet(nn.Module):
         if targets is not None:
             raise NotImplementedError("training branch (models.py:173-222) is out of scope")
         eng = self.engine(max_batch=x.shape[0])
-        return eng.forward_nchw(x).cpu()
+        out = eng.forward_nchw(x)
+        eng.check()
+        return out.cpu()
 
     # ------------------------------------------------------------ weight files
     def load_darknet_weights(self, weights_path):
@@ -151,6 +154,7 @@ class Darknet(nn.Module):
             blob = np.fromfile(fh, dtype=np.float32)
         cutoff = 75 if "darknet53.conv.74" in weights_path else None
         pos = 0
+        self._weights_epoch += 1
 
         def take(param):
             nonlocal pos

@@ -60,7 +60,7 @@ def synthetic_state_dict(model, seed=0, conf_bias=None):
         nxt = defs[layer + 1]["type"] if layer + 1 < len(defs) else ""
         if "conv_" in key and leaf == "weight":
             fan_in = t[0].numel()
-            gain = 2.0 / 1.01                       # variance-preserving for leaky(0.1)
+            gain = 0.75 * 2.0 / 1.01                # slightly contracting for leaky(0.1) + random BN stats
             if nxt == "shortcut":
                 gain *= 0.1                         # keep the residual stream from exploding
             if nxt == "yolo":

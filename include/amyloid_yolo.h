@@ -1,0 +1,123 @@
+/*
+ * amyloid_yolo.h — C ABI of the B200 (sm_100a) tile-detection engine.
+ *
+ * The reference (keiserlab/amyloid-yolo-paper) is pure Python on PyTorch and has
+ * no FFI of its own; its boundary for this path is the Python API
+ *   Darknet(config_path).forward(x)              models.py:228-255
+ *   non_max_suppression(pred, conf, nms)         utils/utils.py:235-273
+ *   rescale_boxes(boxes, dim, shape)             utils/utils.py:36-50
+ *   mergeDetections(detections)                  core.py:366-423
+ * The entry points below are what a ctypes shim bound to those functions calls
+ * (see INTEGRATION.md for the stub a maintainer would add to the reference).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative AY_E* code on failure;
+ *     ay_last_error() returns a thread-local message for the last failure;
+ *   - nothing throws across the boundary; the caller owns every buffer;
+ *   - pointers are DEVICE pointers unless the name ends in _h (host);
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it
+ *     unless stated otherwise;
+ *   - one ay_ctx per GPU; a ctx is not thread-safe, distinct ctxs are independent.
+ */
+#ifndef AMYLOID_YOLO_H_
+#define AMYLOID_YOLO_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AY_OK            0
+#define AY_EINVAL       -1   /* bad argument / unsupported configuration      */
+#define AY_ECUDA        -2   /* a CUDA runtime or driver call failed          */
+#define AY_ENOMEM       -3
+#define AY_ESTATE       -4   /* call sequence violated (e.g. forward before finalize) */
+#define AY_ECAPACITY    -5   /* a per-tile capacity was exceeded; see message */
+
+typedef struct ay_ctx ay_ctx;
+
+/* layer kinds, one per cfg block type handled by models.py:16-83 */
+enum { AY_CONV = 0, AY_MAXPOOL = 1, AY_UPSAMPLE = 2, AY_ROUTE = 3, AY_SHORTCUT = 4, AY_YOLO = 5 };
+
+/* input kinds accepted by ay_forward */
+enum { AY_IN_F32_NCHW = 0,    /* [B,3,S,S] float, already /255 and resized (Darknet.forward contract) */
+       AY_IN_U8_HWC   = 1 };  /* [B,H,W,3] uint8 tiles; ToTensor + nearest Resize (utils/transforms.py:89-111) fused into the first conv */
+
+/* activation storage type of the tensor-core path */
+enum { AY_BF16 = 0, AY_FP16 = 1 };
+
+typedef struct ay_layer_desc {
+  int32_t type;             /* AY_CONV ...                                              */
+  int32_t filters;          /* conv: output channels                                    */
+  int32_t size;             /* conv / maxpool: kernel size (conv pad = (size-1)/2)      */
+  int32_t stride;           /* conv / maxpool / upsample                                */
+  int32_t leaky;            /* conv: 1 = LeakyReLU(0.1) after bias, 0 = linear          */
+  int32_t n_src;            /* route: number of sources; shortcut: 1                    */
+  int32_t src[4];           /* ABSOLUTE layer indices (route layers / shortcut from)    */
+  int32_t n_anchors;        /* yolo                                                     */
+  int32_t classes;          /* yolo                                                     */
+  float   anchors[16];      /* yolo: (w,h) pairs already selected by mask, in pixels    */
+} ay_layer_desc;
+
+/* ---- context ------------------------------------------------------------------ */
+int  ay_create(ay_ctx** out, int device);
+int  ay_destroy(ay_ctx* ctx);
+const char* ay_last_error(void);
+int  ay_abi_version(void);
+
+/* ---- network (replaces models.py:16-83 create_modules + 237-255 forward) -------- */
+/* Describe the network; allocates activations for up to max_batch tiles.          */
+int  ay_net_build(ay_ctx* ctx, const ay_layer_desc* layers_h, int n_layers,
+                  int in_channels, int img_size, int max_batch, int act_dtype);
+/* Weights of conv layer `layer` (index into layers_h): OIHW fp32 with BatchNorm
+ * already folded by the caller (w' = w*gamma/sqrt(var+eps), b' = beta-mean*gamma/sqrt(var+eps)),
+ * bias_h has `filters` entries.  Synchronous (host buffers may be freed on return). */
+int  ay_net_set_conv(ay_ctx* ctx, int layer, const float* w_oihw_h, const float* bias_h);
+int  ay_net_finalize(ay_ctx* ctx);
+/* rows (sum A*G*G) and columns (5+C) of the decoded output per tile                */
+int  ay_net_output_shape(ay_ctx* ctx, int* rows, int* cols);
+/* Forward + YOLO decode.  out_decoded: [B, rows, cols] fp32 (xywh, as models.py:161-169). */
+int  ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                float* out_decoded, void* stream);
+/* Debug/test helper: copy the stored output of layer `layer` (conv, maxpool, upsample,
+ * shortcut, route) of the last forward into out_nchw [B,C,H,W] fp32.                */
+int  ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out_nchw, void* stream);
+int  ay_net_layer_shape(ay_ctx* ctx, int layer, int* channels, int* height, int* width);
+/* Which convolution implementation ran for `layer` in the last forward:
+ * 0 = none, 1 = tcgen05 implicit GEMM, 2 = first-layer direct kernel.              */
+int  ay_net_layer_impl(ay_ctx* ctx, int layer);
+/* number of kernels one ay_forward launches for the built network                  */
+int  ay_net_launch_count(ay_ctx* ctx);
+
+/* ---- post-processing ------------------------------------------------------------ */
+/* utils/utils.py:235-273.  pred: [B,N,5+C] fp32 decoded (xywh); columns 0..3 are
+ * rewritten to xyxy IN PLACE (the reference mutates its argument, utils.py:244).
+ * out_rows [B,cap,7] (x1,y1,x2,y2,conf,cls_conf,cls_pred), out_keep [B,cap] original
+ * row index of each kept box, out_counts [B].  cap >= N guarantees no overflow;
+ * tiles with more than `cap` kept boxes set counts to -1 and the call reports
+ * AY_ECAPACITY at the next ay_check().                                              */
+int  ay_nms(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes,
+            float conf_thres, float nms_thres,
+            float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream);
+/* utils/utils.py:36-50 followed (merge != 0) by core.py:366-423, per tile.
+ * rows [B,cap,7] / counts [B] as produced by ay_nms; results in out_rows [B,cap,7]
+ * (row order = the reference's CPython-3.12 set order) and out_counts [B].          */
+int  ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* counts, int batch, int cap,
+                      int current_dim, int orig_h, int orig_w, int merge,
+                      float* out_rows, int32_t* out_counts, void* stream);
+/* bbox_iou (utils/utils.py:202-232, x1y1x2y2=True): iou[i] of box1[i or 0] vs box2[i]. */
+int  ay_bbox_iou(ay_ctx* ctx, const float* box1, int n1, const float* box2, int n2,
+                 float* out_iou, void* stream);
+/* Synchronise `stream` and report asynchronous errors / capacity overflows.         */
+int  ay_check(ay_ctx* ctx, void* stream);
+
+/* ---- test hooks ------------------------------------------------------------------ */
+/* Plain CUDA-core direct convolution over the same padded NHWC buffers (no tensor
+ * cores); used by tests to cross-check the tcgen05 kernel at full size on the GPU.  */
+int  ay_net_use_reference_conv(ay_ctx* ctx, int enable);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AMYLOID_YOLO_H_ */

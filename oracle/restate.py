@@ -108,8 +108,6 @@ def darknet_forward(blocks, state, x, emulate_bf16=False, return_layers=False, r
     def q(t):
         return t.to(torch.bfloat16).to(torch.float32) if emulate_bf16 else t
 
-    if emulate_bf16:
-        x = q(x)
     for i, d in enumerate(defs):
         t = d["type"]
         if t == "convolutional":
@@ -129,11 +127,14 @@ def darknet_forward(blocks, state, x, emulate_bf16=False, return_layers=False, r
                     w = w * s.view(-1, 1, 1, 1)
                     cb = b - mu * s
                 is_head = defs[i + 1]["type"] == "yolo" if i + 1 < len(defs) else False
-                x = F.conv2d(x, q(w), None, int(d["stride"]), (k - 1) // 2) + cb.view(1, -1, 1, 1)
+                # the engine's first layer (Cin=3) runs in fp32 on fp32 weights and input
+                wq = w if (i == 0 and w.shape[1] < 8) else q(w)
+                fused_add = (not is_head) and i + 1 < len(defs) and defs[i + 1]["type"] == "shortcut"
+                x = F.conv2d(x, wq, None, int(d["stride"]), (k - 1) // 2) + cb.view(1, -1, 1, 1)
                 if d["activation"] == "leaky":
                     x = F.leaky_relu(x, 0.1)
-                if not is_head:
-                    x = q(x)
+                if not is_head and not fused_add:
+                    x = q(x)                    # fused shortcut: one rounding after the add
             else:
                 x = F.conv2d(x, w, None if bn else cb, int(d["stride"]), (k - 1) // 2)
                 if bn:
