@@ -1,0 +1,124 @@
+"""Tile-detection pipeline: the body of ``detect.py``'s batch loop as one device-side chain.
+
+Reference flow per batch (``detect.py:88-133``, ``validation.py:333-346``)::
+
+    ImageFolder -> ToTensor -> Resize(416)          utils/transforms.py:89-111
+    model(input_imgs)                               models.py:237-255   (returns a CPU tensor)
+    non_max_suppression(det, conf_thres, nms_thres) utils/utils.py:235-273  (python loop, CPU)
+    rescale_boxes(det, img_size, (H, W))            utils/utils.py:36-50
+    mergeDetections(det)   [--merge_boxes True]     core.py:366-423
+
+Here the decoded tensor never leaves the GPU: ``ay_forward`` (uint8 tiles in, the
+resize fused into the first convolution) -> ``ay_nms`` -> ``ay_rescale_merge`` run
+back to back on one stream, and only ``counts [B]`` plus the first ``kmax`` rows per
+tile are copied back.  Results equal what the reference's functions return on the
+same decoded input (bit-exact, ``tests/test_gpu_parity.py``).
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr())
+
+
+class TileDetector:
+    """Runs forward + NMS + rescale (+ merge) for batches of square uint8 tiles.
+
+    ``model`` is a :class:`amyloid_yolo_paper_b200.models.Darknet` whose weights are
+    already loaded.  ``cap`` bounds the detections kept per tile (the reference has
+    no bound; exceeding it raises ``EngineError(AY_ECAPACITY)`` at the next check
+    instead of truncating silently).
+    """
+
+    def __init__(self, model, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=64, cap=256,
+                 device=None):
+        if not torch.cuda.is_available():
+            raise _lib.EngineUnavailable("no CUDA device: the B200 pipeline has no CPU fallback")
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.model = model
+        self.conf_thres = float(conf_thres)
+        self.nms_thres = float(nms_thres)
+        self.merge_boxes = bool(merge_boxes)
+        self.max_batch = int(max_batch)
+        self.engine = model.engine(device=self.device, max_batch=self.max_batch)
+        self.img_size = self.engine.img_size
+        self.rows, self.cols = self.engine.rows, self.engine.cols
+        self.cap = int(min(cap, self.rows))
+        self.lib = self.engine.lib
+        self.ctx = self.engine.ctx          # NMS / merge scratch lives in the same context as the network
+        B, dev = self.max_batch, self.device
+        self.decoded = torch.empty((B, self.rows, self.cols), dtype=torch.float32, device=dev)
+        self.nms_rows = torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev)
+        self.nms_keep = torch.empty((B, self.cap), dtype=torch.int32, device=dev)
+        self.nms_counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        self.out_rows = torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev)
+        self.out_counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        self.launches_per_batch = 0
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ------------------------------------------------------------------ device side
+    def run_device(self, tiles, original_shape=None):
+        """tiles: CUDA uint8 [B,H,H,3] (B <= max_batch) or CUDA fp32 [B,3,S,S].
+        Enqueues the whole chain on the current stream; returns views
+        ``(rows [B,cap,7], counts [B])`` of internal buffers (valid until the next call)."""
+        B = tiles.shape[0]
+        if B < 1 or B > self.max_batch:
+            raise ValueError("batch %d outside 1..%d" % (B, self.max_batch))
+        if not tiles.is_cuda or not tiles.is_contiguous():
+            raise ValueError("run_device expects a contiguous CUDA tensor")
+        if tiles.dtype == torch.uint8:
+            if tiles.dim() != 4 or tiles.shape[3] != 3 or tiles.shape[1] != tiles.shape[2]:
+                raise ValueError("expected uint8 tiles [B,H,H,3], got %s" % (tuple(tiles.shape),))
+            kind, sh, sw = _lib.AY_IN_U8_HWC, tiles.shape[1], tiles.shape[2]
+        elif tiles.dtype == torch.float32:
+            kind, sh, sw = _lib.AY_IN_F32_NCHW, tiles.shape[2], tiles.shape[3]
+        else:
+            raise ValueError("tiles must be uint8 HWC or float32 NCHW")
+        if original_shape is None:
+            original_shape = (sh, sw)
+        st = self._stream()
+        lib, ctx = self.lib, self.ctx
+        with torch.cuda.device(self.device):
+            _lib.check(lib.ay_forward(ctx, _ptr(tiles), kind, B, sh, sw, _ptr(self.decoded), st))
+            _lib.check(lib.ay_nms(ctx, _ptr(self.decoded), B, self.rows, self.cols - 5, self.conf_thres,
+                                  self.nms_thres, _ptr(self.nms_rows), _ptr(self.nms_keep), _ptr(self.nms_counts),
+                                  self.cap, st))
+            _lib.check(lib.ay_rescale_merge(ctx, _ptr(self.nms_rows), _ptr(self.nms_counts), B, self.cap,
+                                            self.img_size, int(original_shape[0]), int(original_shape[1]),
+                                            1 if self.merge_boxes else 0, _ptr(self.out_rows),
+                                            _ptr(self.out_counts), st))
+        # forward kernels + 4 NMS kernels + 1 rescale/merge kernel
+        self.launches_per_batch = self.engine.launch_count() + 4 + 1
+        return self.out_rows[:B], self.out_counts[:B]
+
+    def check(self):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.ay_check(self.ctx, self._stream()))
+
+    # ------------------------------------------------------------------ host side
+    def detect(self, tiles, original_shape=None):
+        """tiles: host (ideally pinned) or device uint8 [B,H,H,3] / fp32 [B,3,S,S], any B.
+        -> list (len B) of ``[k,7]`` fp32 CPU tensors (x1,y1,x2,y2,conf,cls_conf,cls_pred in
+        original-tile pixels) or ``None`` where nothing was detected — the per-image value
+        ``detect.py:127-133`` ends up with."""
+        out = []
+        for lo in range(0, tiles.shape[0], self.max_batch):
+            chunk = tiles[lo:lo + self.max_batch]
+            if not chunk.is_cuda:
+                chunk = chunk.to(self.device, non_blocking=True)
+            rows, counts = self.run_device(chunk.contiguous(), original_shape)
+            counts_h = counts.cpu()                 # synchronises the stream
+            self.check()
+            kmax = int(counts_h.max()) if counts_h.numel() else 0
+            rows_h = rows[:, :max(kmax, 1)].cpu()
+            for b, k in enumerate(counts_h.tolist()):
+                out.append(rows_h[b, :k].clone() if k > 0 else None)
+        return out

@@ -1,0 +1,93 @@
+"""Whole-slide sweep: tiles sharded over the GPUs of one box, detections gathered.
+
+The reference walks a slide's tiles one by one in a single process
+(``validation.py:80-135``, ``prospective.py:52-93``).  Every tile is independent
+through forward, NMS, rescale and merge, so the sweep shards by tile: rank ``r`` of
+``R`` owns the contiguous block ``shard_range(n_tiles, r, R)``; the only exchange is
+the final gather of per-tile detection lists —
+
+    all_gather(counts int32 [tiles_per_rank])  +  all_gather(rows fp32 [tiles_per_rank, kmax, 7])
+
+over NCCL (NVLink/NVSwitch) on the GPU box, gloo in the CPU tests.  No activation or
+weight traffic; each rank holds a full weight replica.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_tiles, rank, world):
+    """Contiguous block of tile ids owned by ``rank`` (sizes differ by at most one)."""
+    base, extra = divmod(int(n_tiles), int(world))
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def pack_detections(per_tile, kmax=None, device=None):
+    """list of ``[k,7]`` tensors / None -> (rows [T,kmax,7] fp32 zero padded, counts [T] int32)."""
+    counts = torch.tensor([0 if d is None else int(d.shape[0]) for d in per_tile], dtype=torch.int32)
+    kmax = int(kmax if kmax is not None else (int(counts.max()) if len(per_tile) else 0))
+    rows = torch.zeros((len(per_tile), max(kmax, 1), 7), dtype=torch.float32)
+    for t, d in enumerate(per_tile):
+        if d is not None and d.shape[0]:
+            rows[t, :d.shape[0]] = d.to(torch.float32).cpu()
+    if device is not None:
+        rows, counts = rows.to(device), counts.to(device)
+    return rows, counts
+
+
+def unpack_detections(rows, counts):
+    rows, counts = rows.cpu(), counts.cpu().tolist()
+    return [rows[t, :k].clone() if k > 0 else None for t, k in enumerate(counts)]
+
+
+def allgather_detections(rows, counts, n_tiles, group=None):
+    """Gather every rank's ``(rows [t_r,k_r,7], counts [t_r])`` (tensors on the backend's
+    device: CUDA for NCCL, CPU for gloo) into the full sweep on every rank.
+
+    -> (rows [n_tiles, kmax, 7], counts [n_tiles]) in global tile order."""
+    if not (dist.is_available() and dist.is_initialized()):
+        return rows, counts
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    lo, hi = shard_range(n_tiles, rank, world)
+    if counts.shape[0] != hi - lo:
+        raise ValueError("rank %d owns %d tiles but passed %d" % (rank, hi - lo, counts.shape[0]))
+    dev = rows.device
+    per_rank = -(-int(n_tiles) // world)                     # ceil: all_gather needs equal shapes
+    # agree on the row padding: one tiny all_reduce(MAX)
+    kmax = torch.tensor([rows.shape[1] if rows.shape[0] else 1], dtype=torch.int32, device=dev)
+    dist.all_reduce(kmax, op=dist.ReduceOp.MAX, group=group)
+    k = int(kmax.item())
+    send_counts = torch.zeros((per_rank,), dtype=torch.int32, device=dev)
+    send_counts[:hi - lo] = counts
+    send_rows = torch.zeros((per_rank, k, 7), dtype=torch.float32, device=dev)
+    if hi > lo:
+        send_rows[:hi - lo, :rows.shape[1]] = rows
+    all_counts = torch.empty((world * per_rank,), dtype=torch.int32, device=dev)
+    all_rows = torch.empty((world * per_rank, k, 7), dtype=torch.float32, device=dev)
+    dist.all_gather_into_tensor(all_counts, send_counts, group=group)
+    dist.all_gather_into_tensor(all_rows, send_rows, group=group)
+    # drop the padding tiles of the ranks that own one tile fewer
+    sel = []
+    for r in range(world):
+        rlo, rhi = shard_range(n_tiles, r, world)
+        sel.extend(range(r * per_rank, r * per_rank + (rhi - rlo)))
+    sel = torch.tensor(sel, dtype=torch.long, device=dev)
+    return all_rows.index_select(0, sel), all_counts.index_select(0, sel)
+
+
+def sweep(detector, tile_source, n_tiles, batch, group=None, gather=True):
+    """Run ``detector`` (a :class:`TileDetector`) over this rank's shard of ``n_tiles``.
+
+    ``tile_source(lo, hi)`` returns the tiles ``[lo, hi)`` as a uint8 ``[hi-lo,H,H,3]`` tensor
+    (host or device).  -> (rows, counts) of the whole sweep if ``gather`` else of the shard."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    lo, hi = shard_range(n_tiles, rank, world)
+    per_tile = []
+    for b0 in range(lo, hi, batch):
+        per_tile.extend(detector.detect(tile_source(b0, min(hi, b0 + batch))))
+    dev = detector.device if (dist.is_initialized() and dist.get_backend(group) == "nccl") else None
+    rows, counts = pack_detections(per_tile, device=dev)
+    if gather and world > 1:
+        return allgather_detections(rows, counts, n_tiles, group)
+    return rows, counts

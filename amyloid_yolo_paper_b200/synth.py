@@ -135,7 +135,7 @@ def synthetic_predictions(batch, num_classes=2, seed=5, img=416, grids=GRIDS_416
     return out
 
 
-def synthetic_detections(count, seed=0, extent=1536.0, num_classes=2, overlap=0.5):
+def synthetic_detections(count, seed=0, extent=1536.0, num_classes=2, overlap=0.5, wh=(20, 260), jitter=40):
     """Post-NMS rows [count,7] (x1,y1,x2,y2,conf,cls_conf,cls_pred) in original
     tile coordinates, with a tunable share of overlapping same-class pairs and
     some boxes hanging over the top/left edge (negative coordinates)."""
@@ -144,13 +144,13 @@ def synthetic_detections(count, seed=0, extent=1536.0, num_classes=2, overlap=0.
     for i in range(count):
         if i and rng.random() < overlap:
             j = int(rng.integers(0, i))
-            cx = (rows[j, 0] + rows[j, 2]) / 2 + rng.normal(0, 40)
-            cy = (rows[j, 1] + rows[j, 3]) / 2 + rng.normal(0, 40)
+            cx = (rows[j, 0] + rows[j, 2]) / 2 + rng.normal(0, jitter)
+            cy = (rows[j, 1] + rows[j, 3]) / 2 + rng.normal(0, jitter)
             cls = rows[j, 6] if rng.random() < 0.8 else float(rng.integers(0, num_classes))
         else:
             cx, cy = rng.uniform(-20, extent + 20, 2)
             cls = float(rng.integers(0, num_classes))
-        w, h = rng.uniform(20, 260, 2)
+        w, h = rng.uniform(wh[0], wh[1], 2)
         rows[i] = (cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2,
                    rng.uniform(0.8, 1.0), rng.uniform(0.5, 1.0), cls)
     return rows

@@ -1,0 +1,187 @@
+"""Host-side logic that needs no GPU: cfg parsing, module/parameter naming, weight-file
+formats, the C-ABI library's exports, loud failure without a device, CLI flags."""
+import ctypes
+import os
+import re
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import ROOT, write_mini_cfg
+from amyloid_yolo_paper_b200 import _lib, synth
+from amyloid_yolo_paper_b200.config import ensure_cfg
+from amyloid_yolo_paper_b200.models import Darknet
+from amyloid_yolo_paper_b200.utils.parse_config import parse_data_config, parse_model_config
+
+
+def test_generated_cfgs_equal_reference_blocks(golden):
+    """config/__init__.py regenerates the reference's cfg files; the parsed block lists must be
+    identical to the reference parser's output on the reference's files (tests/golden/cfg_blocks.json)."""
+    want = golden("cfg_blocks.json")
+    for name in ("yolov3-custom", "yolov3-tiny", "yolov3"):
+        got = parse_model_config(ensure_cfg(name))
+        ref = want[name]
+        assert len(got) == len(ref), name
+        for i, (a, b) in enumerate(zip(got[1:], ref[1:])):
+            a = {k: v for k, v in a.items()}
+            b = {k: v for k, v in b.items()}
+            if a["type"] == "yolo":                       # whitespace inside the anchor list differs harmlessly
+                for k in ("anchors", "mask"):
+                    a[k] = a[k].replace(" ", "")
+                    b[k] = b[k].replace(" ", "")
+            assert a == b, (name, i, a, b)
+        for k in ("channels", "height", "width"):
+            assert got[0][k] == ref[0][k]
+
+
+def test_parser_quirks(tmp_path):
+    p = tmp_path / "q.cfg"
+    p.write_text("[net]\nheight=64\n# comment\n\n[convolutional]\nfilters = 8 \nsize=1\n[convolutional]\nbatch_normalize=1\nfilters=4\n")
+    blocks = parse_model_config(str(p))
+    assert blocks[1]["batch_normalize"] == 0 and blocks[1]["filters"] == "8"      # int 0 default, strings otherwise
+    assert blocks[2]["batch_normalize"] == "1"
+    d = tmp_path / "x.data"
+    d.write_text("classes= 3\ntrain=a.txt\n")
+    opt = parse_data_config(str(d))
+    assert opt["classes"] == "3" and opt["gpus"] == "0,1,2,3" and opt["num_workers"] == "10"
+
+
+def test_custom_network_layout_and_state_dict_keys():
+    m = Darknet(ensure_cfg("yolov3-custom"))
+    assert len(m.module_defs) == 107 and len(m.module_list) == 107 and len(m.yolo_layers) == 3
+    sd = m.state_dict()
+    assert len(sd) == 438
+    assert "module_list.0.conv_0.weight" in sd and "module_list.0.batch_norm_0.running_var" in sd
+    assert "module_list.81.conv_81.bias" in sd and "module_list.105.conv_105.bias" in sd
+    assert sd["module_list.105.conv_105.weight"].shape == (21, 256, 1, 1)
+    assert [y.anchors for y in m.yolo_layers] == [[(116, 90), (156, 198), (373, 326)], [(30, 61), (62, 45), (59, 119)],
+                                                  [(10, 13), (16, 30), (33, 23)]]
+    assert m.img_size == 416 and m.seen == 0 and m.header_info.tolist() == [0, 0, 0, 0, 0]
+
+
+def test_param_count_matches_survey():
+    m = Darknet(ensure_cfg("yolov3-custom"))
+    total = sum(v.numel() for k, v in m.state_dict().items() if "num_batches_tracked" not in k)
+    assert total == 61581727
+    t = Darknet(ensure_cfg("yolov3-tiny"))
+    total = sum(v.numel() for k, v in t.state_dict().items() if "num_batches_tracked" not in k)
+    assert total == 8858734
+
+
+def test_pth_roundtrip_and_darknet_weights_roundtrip(tmp_path):
+    cfg = write_mini_cfg(tmp_path)
+    a = Darknet(cfg, img_size=64)
+    synth.synthetic_state_dict(a, seed=3)
+    pth = str(tmp_path / "ckpt.pth")
+    torch.save(a.state_dict(), pth)
+    b = Darknet(cfg, img_size=64)
+    missing = b.load_state_dict(torch.load(pth))
+    assert not missing.missing_keys and not missing.unexpected_keys
+    a.seen = 12345
+    wpath = str(tmp_path / "mini.weights")
+    a.save_darknet_weights(wpath)
+    n_float = sum(v.numel() for k, v in a.state_dict().items() if "num_batches_tracked" not in k)
+    assert os.path.getsize(wpath) == 20 + 4 * n_float                             # int32[5] header + fp32 stream
+    c = Darknet(cfg, img_size=64)
+    c.load_darknet_weights(wpath)
+    assert int(c.seen) == 12345
+    for (k, v), (_, w) in zip(a.state_dict().items(), c.state_dict().items()):
+        if "num_batches_tracked" not in k:
+            assert torch.equal(v, w), k
+    # stream order per conv: bn.bias, bn.weight, running_mean, running_var, conv.weight (models.py:276-300)
+    blob = np.fromfile(wpath, dtype=np.float32, offset=20)
+    sd = a.state_dict()
+    assert np.array_equal(blob[:32], sd["module_list.0.batch_norm_0.bias"].numpy())
+    assert np.array_equal(blob[32:64], sd["module_list.0.batch_norm_0.weight"].numpy())
+    assert np.array_equal(blob[128:128 + 864], sd["module_list.0.conv_0.weight"].numpy().reshape(-1))
+
+
+def test_tiny_weights_file_size():
+    """save_darknet_weights on yolov3-tiny is 35 434 956 B = the real yolov3-tiny.weights size."""
+    t = Darknet(ensure_cfg("yolov3-tiny"))
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "t.weights")
+        t.save_darknet_weights(p)
+        assert os.path.getsize(p) == 35434956
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    names = _lib.exported_symbols()
+    assert len(names) >= 18
+    for n in names:
+        assert hasattr(lib, n), n
+    assert lib.ay_abi_version() >= 1
+    # no torch / C++ types in the header's signatures
+    text = open(_lib.HEADER).read()
+    assert "at::" not in text and "torch" not in text and "std::" not in text
+    assert set(_lib._PROTOTYPES) | {"ay_last_error"} == set(names)
+
+
+def test_layer_desc_struct_matches_header():
+    text = open(_lib.HEADER).read()
+    body = re.search(r"typedef struct ay_layer_desc \{(.*?)\} ay_layer_desc;", text, re.S).group(1)
+    fields = re.findall(r"^\s*(int32_t|float)\s+(\w+)(?:\[(\d+)\])?;", body, re.M)
+    assert [f[1] for f in fields] == [f[0] for f in _lib.LayerDesc._fields_]
+    size = sum(4 * (int(n) if n else 1) for _, _, n in fields)
+    assert ctypes.sizeof(_lib.LayerDesc) == size
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_product_fails_loudly_without_gpu(tmp_path):
+    """No CPU fallback anywhere on the product path."""
+    from amyloid_yolo_paper_b200.core import mergeDetections
+    from amyloid_yolo_paper_b200.utils.utils import bbox_iou, non_max_suppression, rescale_boxes
+    m = Darknet(write_mini_cfg(tmp_path), img_size=64)
+    with pytest.raises(_lib.EngineUnavailable):
+        m(torch.zeros(1, 3, 64, 64))
+    with pytest.raises(_lib.EngineUnavailable):
+        non_max_suppression(torch.zeros(1, 10, 7), 0.5, 0.4)
+    with pytest.raises(_lib.EngineUnavailable):
+        mergeDetections(torch.zeros(2, 7))
+    with pytest.raises(_lib.EngineUnavailable):
+        rescale_boxes(torch.zeros(2, 7), 416, (1536, 1536))
+    with pytest.raises(_lib.EngineUnavailable):
+        bbox_iou(torch.zeros(1, 4), torch.zeros(3, 4))
+    handle = ctypes.c_void_p()
+    assert _lib.load().ay_create(ctypes.byref(handle), 0) != 0
+    assert b"no CPU fallback" in _lib.load().ay_last_error() or b"CUDA" in _lib.load().ay_last_error()
+    with pytest.raises(NotImplementedError):
+        m(torch.zeros(1, 3, 64, 64), targets=torch.zeros(1, 6))
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "amyloid_yolo_paper_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", text, re.M), f
+                assert "/root/reference" not in text, f
+
+
+def test_detect_cli_flags_match_reference():
+    from amyloid_yolo_paper_b200.detect import build_parser, pad_square
+    p = build_parser()
+    d = p.parse_args([])
+    assert (d.conf_thres, d.nms_thres, d.batch_size, d.n_cpu, d.img_size) == (0.8, 0.4, 1, 0, 416)
+    assert d.image_folder == "data/samples" and d.model_def == "config/yolov3.cfg"
+    assert d.weights_path == "weights/yolov3.weights" and d.class_path == "data/coco.names"
+    assert d.merge_boxes is None and d.checkpoint_model is None
+    o = p.parse_args(["--merge_boxes", "True", "--img_size", "416", "--conf_thres", "0.8", "--nms_thres", "0.4"])
+    assert o.merge_boxes == "True"                       # string, compared with "True" (detect.py:132)
+    img = np.ones((4, 7, 3), np.uint8)
+    sq = pad_square(img)
+    assert sq.shape == (7, 7, 3) and sq[:1].sum() == 0 and sq[1:5].sum() == 4 * 7 * 3 and sq[5:].sum() == 0
+
+
+def test_shard_ranges_cover_all_tiles():
+    from amyloid_yolo_paper_b200.sweep import shard_range
+    for n in (0, 1, 7, 8, 100000, 100003):
+        for w in (1, 2, 4, 8):
+            spans = [shard_range(n, r, w) for r in range(w)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(spans[i][1] == spans[i + 1][0] for i in range(w - 1))
+            assert max(b - a for a, b in spans) - min(b - a for a, b in spans) <= 1
