@@ -72,6 +72,43 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvG
 int conv_gemm_smem_bytes(int BN, int BK, int stages);
 int conv_gemm_pick_stages(int BN, int BK);
 
+// Parameters of one CTA-pair implicit-GEMM launch (conv_gemm2_sm100.cu).  A "group" is one A box
+// (a_rows rows x BK channels) together with the G weight tiles of the taps that read it.
+struct ConvGemm2Params {
+  int P;                 // output rows to compute: batch * (H+2) * (W+2)
+  int num_m_tiles;       // ceil(P / 256): one tile per CTA pair
+  int num_n_tiles;       // Cout_padded / BN
+  int n_groups;          // A boxes per k-block (3x3 s1 with tap reuse: 3; otherwise = number of taps)
+  int G;                 // taps per group (3 with reuse, else 1)
+  int kb_per_tap;        // Cin_padded / BK
+  int a_row_off[9];      // row offset of group g's A box
+  int a_rows;            // rows of the A box (128, or 130 with reuse)
+  int BN, BK;            // BN: N of the pair tile (each CTA loads BN/2 weight rows)
+  int num_stages;
+  int base_off_mode;     // 1: descriptor base offset = rows skipped (PTX rule); 0: always 0
+  int b_swap;            // debug: swap which CTA loads which half of the weight tile
+  int dbg;               // ablation bits (AY_DBG): 1 no MMA, 2 no operand TMA, 4 no output store, 8 no residual
+  int Hp, Wp;            // padded output size (halo test)
+  int out_pitch;
+  void* out;
+  const float* bias;
+  const void* residual;
+  int res_pitch;
+  int leaky;
+  int is_fp16;
+  int head;
+  float* dec_out;
+  int dec_rows_total, dec_row_off, dec_cols, n_anchors, cout;
+  float stride;
+  float anchor_w[8], anchor_h[8];
+  unsigned int* err_flag;
+};
+int launch_conv_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut,
+                      const CUtensorMap& tmRes, const CUtensorMap& tmResPF, const ConvGemm2Params& p, int num_sms,
+                      cudaStream_t stream);
+int conv_gemm2_stage_bytes(int BN, int BK, int G, int a_rows);
+int conv_gemm2_pick_stages(int BN, int BK, int G, int a_rows);
+
 // aux_kernels.cu ------------------------------------------------------------
 struct FirstConvParams {
   const void* in; int in_kind; int batch; int S; int src_h, src_w;

@@ -1,0 +1,514 @@
+// Implicit-GEMM convolution for sm_100a, CTA-pair version:
+//   TMA -> shared memory -> tcgen05.mma.cta_group::2 (UMMA 256 x BN x 16) -> TMEM -> fused epilogue.
+//
+// Replaces, for the whole network, the reference's per-block
+//   nn.Conv2d + nn.BatchNorm2d + nn.LeakyReLU            (models.py:26-45)
+//   shortcut add                                         (models.py:246-248)
+//   YOLOLayer inference decode                           (models.py:137-169)
+//
+// Formulation (see ay_common.h): activations are zero-haloed NHWC rows, so for output
+// row m and filter tap t the input row is m + a_row_off[t] and the convolution is
+//   out[m, n] = epi( sum_t sum_c A[m + a_row_off[t], c] * W[n, t*Cin + c] ).
+//
+// Why a CTA pair: with one CTA per 128 x 256 tile every 64-channel k-block moves 48 KB
+// from L2 into shared memory for 512 tensor-pipe cycles (94 B/clk/SM, x148 SMs = twice what
+// the L2 fabric delivers) and the MMA reads A and B out of the same shared memory the TMA is
+// filling.  Here two CTAs of a cluster own one 256 x BN tile: each loads its own 128 rows of A
+// and HALF of the weight tile, and the leader CTA issues cta_group::2 MMAs that read both halves.
+//
+// Tap reuse: for a 3x3/stride-1 layer the three kw taps of one kh are the same A rows shifted
+// by one row.  One TMA box of 130 rows serves all three: the MMA descriptor of tap kw starts kw
+// rows (kw*128 B) into the box, which the 128-byte swizzle allows through the descriptor's
+// base-offset field.  Per (kh, 64-channel block) a CTA therefore loads 130 rows of A once and
+// three half weight tiles, instead of three full A tiles and three full weight tiles.
+//
+// Kernel shape: persistent, one CTA per SM, clusters of 2, 192 threads per CTA:
+//   warp 0   : TMA producer (one lane, in both CTAs; all loads signal the LEADER's full barrier)
+//   warp 1   : tcgen05.mma issuer (one lane, leader CTA only); tcgen05.commit multicast to both CTAs
+//   warps 2-5: epilogue, one TMEM lane quarter each (tcgen05.ld 32x32b.x32), in both CTAs
+// TMEM holds two BN-column accumulators so the epilogue of tile i overlaps the main loop of i+1.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "ay_common.h"
+
+namespace ay {
+namespace {
+
+constexpr int kRowsPerCta = 128;
+constexpr int kThreads2 = 192;
+constexpr unsigned long long kSpinLimit = 6000000000ull;  // ~3 s: trap instead of hanging the GPU
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void bar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bar_arrive_remote(uint32_t cluster_bar) {
+  // default semantics (release at CTA scope): a .release.cluster here compiles to MEMBAR.ALL.GPU + ERRBAR,
+  // which cost 16 % of all stall samples; the TMEM hand-over only needs tcgen05.fence::before_thread_sync
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint32_t bar, uint32_t parity, unsigned int* err_flag, uint32_t code) {
+  uint32_t done = 0;
+  unsigned long long t0 = 0;
+  uint32_t spins = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if ((++spins & 0xFFF) == 0) {
+      unsigned long long now = clock64();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > kSpinLimit) {
+        if (err_flag) atomicExch(err_flag, 0xDEAD0100u | code);
+        __trap();
+      }
+    }
+  }
+}
+// 2-D tiled TMA load issued by either CTA of the pair; completion bytes go to `cluster_bar`
+// (an mbarrier of the leader CTA, shared::cluster address).
+__device__ __forceinline__ void tma_load_pair(const CUtensorMap* map, uint32_t cluster_bar, uint32_t dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(cluster_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma2_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// arrive on the mbarrier at the same shared-memory offset in both CTAs once all prior MMAs retire
+__device__ __forceinline__ void umma2_commit(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_load32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major operand tile, rows of `row_bytes` (128 -> SWIZZLE_128B, 64 -> SWIZZLE_64B), 8-row groups
+// contiguous (SBO = 8 rows).  `base_off` = (start address >> 7) & 7 when the start is not aligned to the
+// 1024-byte swizzle pattern (tap reuse starts 1 or 2 rows into the box).
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t row_bytes, uint32_t base_off) {
+  const uint64_t layout = (row_bytes == 128) ? 2ull : 4ull;
+  const uint64_t sbo = (8u * row_bytes) >> 4;
+  return (uint64_t)((saddr >> 4) & 0x3FFFu) | (sbo << 32) | (1ull << 46) | ((uint64_t)(base_off & 7u) << 49) | (layout << 61);
+}
+
+__device__ __forceinline__ uint32_t pack_pair(float lo, float hi, int is_fp16) {
+  if (is_fp16) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+  __nv_bfloat162 b = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&b);
+}
+__device__ __forceinline__ float2 unpack_pair(uint32_t w, int is_fp16) {
+  if (is_fp16) return __half22float2(*reinterpret_cast<__half2*>(&w));
+  return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
+}
+__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+// ---- epilogue staging: 32 rows x 32 channels (64-byte rows, TMA SWIZZLE_64B layout) per warp, 3 buffers ----
+constexpr uint32_t kStageBufBytes = 32 * 64;
+constexpr int kStageBufs = 3;
+constexpr uint32_t kStagingBytes = 4 * kStageBufs * kStageBufBytes;   // 24 KB per CTA
+constexpr int kBiasFloats = 1024;
+
+__device__ __forceinline__ void tma_load_local(const CUtensorMap* map, uint32_t bar, uint32_t dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_prefetch_l2(const CUtensorMap* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1)
+               : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void lds128(uint32_t addr, uint4& v) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
+conv_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes,
+                  const __grid_constant__ CUtensorMap tmResPF, const __grid_constant__ ConvGemm2Params p) {
+  // shared memory: [S pipeline stages][epilogue staging 24 KB][mbarriers][tmem slot][bias]
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_addr(smem_raw) + 1023u) & ~1023u;
+  const uint32_t row_bytes = p.BK * 2;
+  const uint32_t a_region = (uint32_t)((p.a_rows + 7) & ~7) * row_bytes;   // multiple of 1024 for both BK
+  const uint32_t b_tile = (uint32_t)(p.BN / 2) * row_bytes;
+  const uint32_t stage_bytes = a_region + p.G * b_tile;
+  const uint32_t tx_bytes = (uint32_t)p.a_rows * row_bytes + p.G * b_tile;  // what one CTA's TMA loads deliver
+  const int S = p.num_stages;
+  const uint32_t staging_base = smem_base + S * stage_bytes;
+  const uint32_t bar_base = staging_base + kStagingBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * S + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + 2 + a); };
+  auto res_bar = [&](int q, int b) { return bar_base + 8u * (2 * S + 4 + q * kStageBufs + b); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * S + 4 + 4 * kStageBufs);
+  // whole-layer bias staged once: with this much shared memory the L1 is ~1 KB, so a global bias load
+  // would be an L2 round trip in the middle of the epilogue's dependency chain
+  float* s_bias = reinterpret_cast<float*>(smem_raw + (tmem_slot - smem_addr(smem_raw)) + 16u);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_rank();
+  const bool leader = rank == 0;
+  const uint32_t tmem_cols = (p.BN <= 16) ? 32u : (p.BN <= 32) ? 64u : (p.BN <= 64) ? 128u : (p.BN <= 128) ? 256u : 512u;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmOut)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmRes)) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < S; ++s) {
+      bar_init(full_bar(s), 1);     // leader's copy is the one in use: 1 arrive.expect_tx + bytes of both CTAs
+      bar_init(empty_bar(s), 1);    // tcgen05.commit multicast
+    }
+    for (int a = 0; a < 2; ++a) {
+      bar_init(tfull_bar(a), 1);    // tcgen05.commit multicast
+      bar_init(tempty_bar(a), 8);   // leader's copy: 4 epilogue warps x 2 CTAs
+    }
+    for (int q = 0; q < 4; ++q)
+      for (int b = 0; b < kStageBufs; ++b) bar_init(res_bar(q, b), 1);   // residual TMA loads, per epilogue warp
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  for (int i = threadIdx.x; i < p.num_n_tiles * p.BN; i += kThreads2) s_bias[i] = __ldg(p.bias + i);
+  __syncthreads();
+  fence_before();
+  cluster_sync_all();
+  fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  const int total_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int n_clusters = gridDim.x >> 1;
+  const int first_tile = blockIdx.x >> 1;
+  const int units = p.n_groups * p.kb_per_tap;      // pipeline stages consumed per tile
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const int b_rank = p.b_swap ? (int)(rank ^ 1u) : (int)rank;
+      const bool has_res = p.residual != nullptr && !(p.dbg & 8);
+      // The residual tile (128 rows x BN channels of this CTA) is pulled into L2 one tile ahead: the epilogue's
+      // small TMA loads then see L2 latency instead of HBM latency, with no shared-memory cost for the bytes in flight.
+      if (has_res && first_tile < total_tiles)
+        tma_prefetch_l2(&tmResPF, (first_tile % p.num_n_tiles) * p.BN,
+                        (first_tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta);
+      for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+        const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
+        const int n0 = (tile % p.num_n_tiles) * p.BN + b_rank * (p.BN / 2);
+        if (has_res && tile + n_clusters < total_tiles) {
+          const int nt = tile + n_clusters;
+          tma_prefetch_l2(&tmResPF, (nt % p.num_n_tiles) * p.BN, (nt / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta);
+        }
+        for (int g = 0; g < p.n_groups; ++g) {
+          const int arow = m0 + p.a_row_off[g];
+          for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+            bar_wait(empty_bar(stage), phase ^ 1u, p.err_flag, 1);
+            const uint32_t lead_full = map_to_cta(full_bar(stage), 0);
+            if (p.dbg & 2) {                                   // ablation: no operand loads
+              if (leader) bar_expect_tx(full_bar(stage), 0u);
+              if (++stage == S) { stage = 0; phase ^= 1u; }
+              continue;
+            }
+            if (leader) bar_expect_tx(full_bar(stage), 2u * tx_bytes);
+            const uint32_t sa = smem_base + stage * stage_bytes;
+            tma_load_pair(&tmA, lead_full, sa, kb * p.BK, arow);
+            for (int j = 0; j < p.G; ++j)
+              tma_load_pair(&tmB, lead_full, sa + a_region + j * b_tile, ((g * p.G + j) * p.kb_per_tap + kb) * p.BK, n0);
+            if (++stage == S) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader && lane == 0) {
+      // instruction descriptor: D=f32, A/B = bf16|f16, both K-major, N = BN, M = 256 (pair)
+      const uint32_t fmt = p.is_fp16 ? 0u : 1u;
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(p.BN >> 3) << 17) |
+                             ((uint32_t)((2 * kRowsPerCta) >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      const int ksteps = p.BK >> 4;
+      for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+        bar_wait(tempty_bar(acc), acc_phase ^ 1u, p.err_flag, 2);
+        fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.BN);
+        for (int it = 0; it < units; ++it) {
+          bar_wait(full_bar(stage), phase, p.err_flag, 3);
+          fence_after();
+          const uint32_t sa = smem_base + stage * stage_bytes;
+          for (int j = 0; j < p.G; ++j) {
+            // tap j of the group starts j rows into the A box; the swizzle is a function of the absolute
+            // shared-memory address, so the descriptor's base-offset field stays 0 (measured: base_off_mode 1 is wrong)
+            const uint64_t adesc = smem_desc(sa + j * row_bytes, row_bytes, p.base_off_mode ? (uint32_t)j : 0u);
+            const uint64_t bdesc = smem_desc(sa + a_region + j * b_tile, row_bytes, 0u);
+            for (int k = 0; k < ksteps && !(p.dbg & 1); ++k)
+              umma2_f16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((it | j | k) != 0));
+          }
+          umma2_commit(empty_bar(stage));   // frees this stage in both CTAs
+          if (++stage == S) { stage = 0; phase ^= 1u; }
+        }
+        umma2_commit(tfull_bar(acc));       // accumulator complete -> both epilogues
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ---------------- epilogue: warps 2..5, TMEM lane quarter = warp % 4 ----------------
+    // Global traffic goes through the TMA only: a thread-per-row ld/st.global touches 32 different
+    // lines per warp instruction and the LSU serialises them (measured: the epilogue, not the MMA,
+    // bounded every layer).  Each warp owns three 32-row x 32-channel staging buffers: the residual
+    // tile is TMA-loaded into one while the previous chunk is processed, the result is written back
+    // in place and TMA-stored.
+    const int quarter = warp & 3;
+    const int row_in_tile = quarter * 32 + lane;
+    const uint32_t lane_addr = ((uint32_t)(quarter * 32)) << 16;
+    const uint32_t stg = staging_base + (uint32_t)quarter * (kStageBufs * kStageBufBytes);
+    const uint32_t my_row = (uint32_t)lane * 64u;
+    const uint32_t my_xor = ((uint32_t)lane >> 1) & 3u;          // SWIZZLE_64B: 16-byte chunk ^= (row / 2) % 4
+    const int hw = p.Hp * p.Wp;
+    const bool has_res = p.residual != nullptr && !(p.dbg & 8);
+    const int nchunks = p.BN >> 5;
+    uint32_t cid = 0;                                            // running chunk counter -> buffer and barrier phase
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+      const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
+      const int n0 = (tile % p.num_n_tiles) * p.BN;
+      const int row0 = m0 + quarter * 32;                        // first of this warp's 32 rows
+      const int m = m0 + row_in_tile;
+      const bool in_range = m < p.P;
+      const int img = m / hw;
+      const int pix = m - img * hw;
+      const int yy = pix / p.Wp;
+      const int xx = pix - yy * p.Wp;
+      const bool halo = (yy == 0) | (yy == p.Hp - 1) | (xx == 0) | (xx == p.Wp - 1);
+      const bool zero_row = halo | !in_range;
+
+      if (!p.head) {
+        if (has_res && lane == 0) {                              // residual of chunk 0, long before the MMAs finish
+          bulk_wait_read<2>();
+          const uint32_t b = cid % kStageBufs;
+          bar_expect_tx(res_bar(quarter, b), kStageBufBytes);
+          tma_load_local(&tmRes, res_bar(quarter, b), stg + b * kStageBufBytes, n0, row0);
+        }
+        bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
+        fence_after();
+        const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
+        for (int c = 0; c < nchunks; ++c, ++cid) {
+          const uint32_t b = cid % kStageBufs;
+          const uint32_t buf = stg + b * kStageBufBytes;
+          uint32_t v[32];
+          tmem_load32(t_acc + (uint32_t)(c * 32), v);
+          if (has_res) {
+            if (c + 1 < nchunks && lane == 0) {                  // next chunk's residual into the buffer stored 2 chunks ago
+              bulk_wait_read<1>();
+              const uint32_t b1 = (cid + 1) % kStageBufs;
+              bar_expect_tx(res_bar(quarter, b1), kStageBufBytes);
+              tma_load_local(&tmRes, res_bar(quarter, b1), stg + b1 * kStageBufBytes, n0 + (c + 1) * 32, row0);
+            }
+            bar_wait(res_bar(quarter, b), (cid / kStageBufs) & 1u, p.err_flag, 5);
+          } else {
+            if (lane == 0) bulk_wait_read<2>();                  // the store that last read this buffer (3 chunks ago)
+            __syncwarp();
+          }
+          const float4* bias4 = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {                          // 8 channels = one 16-byte chunk of my row
+            const uint32_t addr = buf + my_row + (((uint32_t)q ^ my_xor) << 4);
+            float f[8];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const float4 bb = bias4[2 * q + h];
+              f[4 * h + 0] = __uint_as_float(v[8 * q + 4 * h + 0]) + bb.x;
+              f[4 * h + 1] = __uint_as_float(v[8 * q + 4 * h + 1]) + bb.y;
+              f[4 * h + 2] = __uint_as_float(v[8 * q + 4 * h + 2]) + bb.z;
+              f[4 * h + 3] = __uint_as_float(v[8 * q + 4 * h + 3]) + bb.w;
+            }
+            if (p.leaky) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = f[e] > 0.f ? f[e] : 0.1f * f[e];
+            }
+            if (has_res) {
+              uint4 r;
+              lds128(addr, r);
+              const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 rr = unpack_pair(rw[e], p.is_fp16);
+                f[2 * e] += rr.x;
+                f[2 * e + 1] += rr.y;
+              }
+            }
+            uint4 o;
+            o.x = pack_pair(f[0], f[1], p.is_fp16);
+            o.y = pack_pair(f[2], f[3], p.is_fp16);
+            o.z = pack_pair(f[4], f[5], p.is_fp16);
+            o.w = pack_pair(f[6], f[7], p.is_fp16);
+            if (zero_row) o = make_uint4(0u, 0u, 0u, 0u);
+            sts128(addr, o);
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0 && !(p.dbg & 4)) tma_store_2d(&tmOut, buf, n0 + c * 32, row0);
+        }
+      } else {
+        // fused YOLOLayer decode (models.py:137-169): channel ch = a*(5+C) + f
+        bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
+        fence_after();
+        const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
+        const int G = p.Wp - 2;
+        const int gx = xx - 1, gy = yy - 1;
+        float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols +
+                       ((size_t)gy * G + gx) * p.dec_cols;
+        const size_t a_step = (size_t)G * G * p.dec_cols;
+        int a = (n0) / p.dec_cols, f = n0 - a * p.dec_cols;      // running (anchor, field) of channel ch
+        for (int c = 0; c < nchunks; ++c) {
+          uint32_t v[32];
+          tmem_load32(t_acc + (uint32_t)(c * 32), v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int ch = n0 + c * 32 + j;
+            if (ch < p.cout && in_range && !halo) {
+              const float t = __uint_as_float(v[j]) + s_bias[ch];
+              float r;
+              if (f == 0) r = __fmul_rn(__fadd_rn(sigmoid_acc(t), (float)gx), p.stride);
+              else if (f == 1) r = __fmul_rn(__fadd_rn(sigmoid_acc(t), (float)gy), p.stride);
+              else if (f == 2) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_w[a]), p.stride);
+              else if (f == 3) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_h[a]), p.stride);
+              else r = sigmoid_acc(t);
+              obase[(size_t)a * a_step + f] = r;
+            }
+            if (++f == p.dec_cols) { f = 0; ++a; }
+          }
+        }
+      }
+      // this warp is done reading the accumulator: one arrival per warp on the LEADER's barrier
+      fence_before();
+      __syncwarp();
+      if (lane == 0) bar_arrive_remote(map_to_cta(tempty_bar(acc), 0));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores have left shared memory and landed
+  }
+
+  // both CTAs must stay resident until the pair's last MMA, commit and remote arrive have landed
+  fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+  }
+}
+
+}  // namespace
+
+int conv_gemm2_stage_bytes(int BN, int BK, int G, int a_rows) {
+  const int row_bytes = BK * 2;
+  return ((a_rows + 7) & ~7) * row_bytes + G * (BN / 2) * row_bytes;
+}
+
+static int conv_gemm2_fixed_smem(int num_stages) {
+  return (int)kStagingBytes + 8 * (2 * num_stages + 4 + 4 * kStageBufs) + 16 + 4 * kBiasFloats + 1024 /*alignment*/;
+}
+
+int conv_gemm2_pick_stages(int BN, int BK, int G, int a_rows) {
+  const int budget = 227 * 1024 - conv_gemm2_fixed_smem(8);
+  int s = budget / conv_gemm2_stage_bytes(BN, BK, G, a_rows);
+  if (s > 8) s = 8;
+  return s;
+}
+
+int launch_conv_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
+                      const CUtensorMap& tmResPF, const ConvGemm2Params& p, int num_sms, cudaStream_t stream) {
+  if (p.BN % 32 != 0 || p.BN < 32 || p.BN > 256 || (p.BK != 32 && p.BK != 64) || p.num_stages < 2 || p.num_stages > 8 ||
+      (p.G != 1 && (p.G != 3 || p.BK != 64)) || p.num_n_tiles * p.BN > kBiasFloats) {
+    set_error("conv_gemm2: unsupported tile BN=%d BK=%d G=%d stages=%d n_tiles=%d", p.BN, p.BK, p.G, p.num_stages,
+              p.num_n_tiles);
+    return AY_EINVAL;
+  }
+  AY_CUDA(cudaFuncSetAttribute(conv_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  const int smem = p.num_stages * conv_gemm2_stage_bytes(p.BN, p.BK, p.G, p.a_rows) + conv_gemm2_fixed_smem(p.num_stages);
+  const int total = p.num_m_tiles * p.num_n_tiles;
+  const int pairs = num_sms / 2;
+  const int grid = 2 * (total < pairs ? total : pairs);
+  conv_gemm2_kernel<<<grid, kThreads2, smem, stream>>>(tmA, tmB, tmOut, tmRes, tmResPF, p);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+}  // namespace ay

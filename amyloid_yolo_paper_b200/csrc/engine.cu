@@ -11,6 +11,7 @@
 #include <cuda_fp16.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -50,7 +51,7 @@ int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // 2-D K-major map over `rows` rows of `inner` 16-bit elements, row pitch `pitch` elements.
 int make_map_2d(CUtensorMap* map, void* base, int inner, long long rows, int pitch, int box_inner, int box_rows,
-                int is_fp16) {
+                int is_fp16, bool swizzle = true) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -60,7 +61,8 @@ int make_map_2d(CUtensorMap* map, void* base, int inner, long long rows, int pit
   cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  const CUtensorMapSwizzle sw = (box_inner * 2 == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  const CUtensorMapSwizzle sw = !swizzle ? CU_TENSOR_MAP_SWIZZLE_NONE
+                                : (box_inner * 2 == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   CUresult r = enc(map, is_fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims,
                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -105,6 +107,9 @@ struct Layer {
   long long plane_rows = 0;
   float* raw_f32 = nullptr;         // reference path scratch for heads
   CUtensorMap tmA, tmB;
+  // CTA-pair kernel (conv_gemm2_sm100.cu)
+  int G = 1, a_rows = 128, stages2 = 0;
+  CUtensorMap tmA2, tmB2, tmOut, tmRes, tmResPF;   // tmOut/tmRes: 32-channel x 32-row boxes for the epilogue's TMA store / residual load
   // yolo
   int dec_row_off = 0;
   // route copy fallback
@@ -124,6 +129,7 @@ struct ay_ctx {
   std::vector<ay::Layer> layers;
   int in_channels = 3, img_size = 416, max_batch = 0, is_fp16 = 0;
   bool built = false, finalized = false, use_ref = false;
+  int gemm_version = 2, base_off_mode = 0, b_swap = 0, dbg = 0;   // AY_GEMM_V / AY_BASE_OFF / AY_B_SWAP (debug overrides)
   int dec_rows = 0, dec_cols = 0;
   int* idx_y = nullptr;               // nearest-resize tables (device), rebuilt when the source size changes
   int* idx_x = nullptr;
@@ -227,6 +233,10 @@ extern "C" int ay_create(ay_ctx** out, int device) {
     return AY_ENOMEM;
   }
   cudaMemset(ctx->err_flag, 0, sizeof(unsigned int));
+  if (const char* e = getenv("AY_GEMM_V")) ctx->gemm_version = atoi(e) == 1 ? 1 : 2;
+  if (const char* e = getenv("AY_BASE_OFF")) ctx->base_off_mode = atoi(e) != 0;
+  if (const char* e = getenv("AY_B_SWAP")) ctx->b_swap = atoi(e) != 0;
+  if (const char* e = getenv("AY_DBG")) ctx->dbg = atoi(e);
   *out = ctx;
   return AY_OK;
 }
@@ -457,12 +467,29 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     AY_TRY(ay::dev_alloc(ctx, &L.w16, (size_t)L.cout_rows * L.ktot * 2, true));
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.cout_rows, true));
     AY_TRY(ay::make_map_2d(&L.tmB, L.w16, L.ktot, L.cout_rows, L.ktot, L.BK, L.BN, ctx->is_fp16));
+    L.G = (L.d.size == 3 && L.d.stride == 1 && L.BK == 64) ? 3 : 1;
+    L.a_rows = L.G == 3 ? 130 : 128;
+    L.stages2 = ay::conv_gemm2_pick_stages(L.BN, L.BK, L.G, L.a_rows);
+    AY_TRY(ay::make_map_2d(&L.tmB2, L.w16, L.ktot, L.cout_rows, L.ktot, L.BK, L.BN / 2, ctx->is_fp16));
     if (L.d.stride == 2) {
       L.plane_rows = ay::padded_rows(max_batch, L.H, L.W);
       AY_TRY(ay::dev_alloc(ctx, &L.planes, (size_t)4 * L.plane_rows * L.cin_p * 2, true));
       AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, L.BK, 128, ctx->is_fp16));
+      AY_TRY(ay::make_map_2d(&L.tmA2, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, L.BK, L.a_rows, ctx->is_fp16));
     } else {
       AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, L.BK, 128, ctx->is_fp16));
+      AY_TRY(ay::make_map_2d(&L.tmA2, in.ptr, L.cin_p, in.rows_alloc, in.pitch, L.BK, L.a_rows, ctx->is_fp16));
+    }
+    if (!L.is_head) {
+      const ActView& tgt = L.fused_shortcut >= 0 ? Ls[L.fused_shortcut].out : L.out;
+      AY_TRY(ay::make_map_2d(&L.tmOut, tgt.ptr, tgt.Cp, tgt.rows_alloc, tgt.pitch, 32, 32, ctx->is_fp16));
+      const ActView& rv = L.residual_src >= 0 ? Ls[L.residual_src].out : tgt;
+      AY_TRY(ay::make_map_2d(&L.tmRes, rv.ptr, rv.Cp, rv.rows_alloc, rv.pitch, 32, 32, ctx->is_fp16));
+      AY_TRY(ay::make_map_2d(&L.tmResPF, rv.ptr, rv.Cp, rv.rows_alloc, rv.pitch, L.BN, 128, ctx->is_fp16, /*swizzle=*/false));
+    } else {
+      L.tmOut = L.tmA2;
+      L.tmRes = L.tmA2;
+      L.tmResPF = L.tmA2;
     }
     if (L.is_head)
       AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.raw_f32),
@@ -597,6 +624,61 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
       AY_TRY(ay::launch_decode(d, st));
     }
     return AY_OK;
+  }
+
+  if (ctx->gemm_version == 2) {
+    ay::ConvGemm2Params q{};
+    q.P = (int)ay::padded_rows(batch, L.H, L.W);
+    q.num_m_tiles = (q.P + 255) / 256;
+    q.num_n_tiles = L.cout_rows / L.BN;
+    q.G = L.G;
+    q.a_rows = L.a_rows;
+    q.kb_per_tap = L.cin_p / L.BK;
+    if (L.d.size == 1) {
+      q.n_groups = 1;
+      q.a_row_off[0] = 0;
+    } else if (L.d.stride == 1) {
+      if (L.G == 3) {
+        q.n_groups = 3;
+        for (int kh = 0; kh < 3; ++kh) q.a_row_off[kh] = (kh - 1) * Wq - 1;
+      } else {
+        q.n_groups = 9;
+        for (int kh = 0; kh < 3; ++kh)
+          for (int kw = 0; kw < 3; ++kw) q.a_row_off[kh * 3 + kw] = (kh - 1) * Wq + (kw - 1);
+      }
+    } else {
+      AY_TRY(ay::launch_s2_gather(in.ptr, in.pitch, L.cin_p / 8, batch, in.H, in.W, L.planes, L.plane_rows, st));
+      ++ctx->launches;
+      q.n_groups = 9;
+      for (int kh = 0; kh < 3; ++kh)
+        for (int kw = 0; kw < 3; ++kw) {
+          const long long off = (long long)((kh & 1) * 2 + (kw & 1)) * L.plane_rows + (kh >> 1) * Wq + (kw >> 1);
+          if (off > 0x7fffffffLL - (1LL << 26)) { set_error("layer %d: batch too large for 32-bit row offsets", i); return AY_EINVAL; }
+          q.a_row_off[kh * 3 + kw] = (int)off;
+        }
+    }
+    q.BN = L.BN; q.BK = L.BK; q.num_stages = L.stages2;
+    q.base_off_mode = ctx->base_off_mode; q.b_swap = ctx->b_swap; q.dbg = ctx->dbg;
+    q.Hp = Hq; q.Wp = Wq;
+    q.bias = L.bias; q.leaky = L.d.leaky; q.is_fp16 = ctx->is_fp16;
+    q.err_flag = ctx->err_flag;
+    if (L.is_head) {
+      q.head = 1;
+      q.dec_out = dec_out; q.dec_rows_total = ctx->dec_rows; q.dec_row_off = Y->dec_row_off;
+      q.dec_cols = ctx->dec_cols; q.n_anchors = Y->d.n_anchors; q.cout = L.C;
+      const double stride = (double)ctx->img_size / (double)L.H;   // models.py:119
+      q.stride = (float)stride;
+      for (int a = 0; a < Y->d.n_anchors; ++a) {
+        q.anchor_w[a] = (float)((double)Y->d.anchors[2 * a] / stride);      // models.py:122-124
+        q.anchor_h[a] = (float)((double)Y->d.anchors[2 * a + 1] / stride);
+      }
+    } else {
+      q.out = target->ptr; q.out_pitch = target->pitch;
+      q.residual = res ? res->ptr : nullptr; q.res_pitch = res ? res->pitch : 0;
+      q.cout = L.C;
+    }
+    ++ctx->launches;
+    return ay::launch_conv_gemm2(L.tmA2, L.tmB2, L.tmOut, L.tmRes, L.tmResPF, q, ctx->num_sms, st);
   }
 
   ay::ConvGemmParams p{};
