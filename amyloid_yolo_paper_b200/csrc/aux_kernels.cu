@@ -240,7 +240,7 @@ __global__ void ref_conv_kernel(RefConvParams p) {
           const int iy = (y - 1) * p.stride + kh - pad + 1, ix = (x - 1) * p.stride + kw - pad + 1;
           if (iy < 0 || iy >= Hp || ix < 0 || ix >= Wp) continue;
           const size_t irow = ((size_t)n * Hp + iy) * Wp + ix;
-          const size_t wrow = (size_t)oc * p.ktot + (size_t)(kh * p.size + kw) * p.Cin_p;
+          const size_t wrow = (size_t)oc * p.ktot + (size_t)(kh * p.size + kw) * p.Cin_k;
           for (int c = 0; c < p.Cin_p; ++c)
             acc = fmaf(ld16(p.in, irow * p.in_pitch + c, p.is_fp16), ld16(p.w, wrow + c, p.is_fp16), acc);
         }

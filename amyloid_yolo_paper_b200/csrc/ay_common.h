@@ -40,24 +40,26 @@ struct ActView {
   long long rows_alloc = 0;  // pixel rows allocated behind ptr (for max_batch)
 };
 
-// Parameters of one implicit-GEMM convolution launch (conv_gemm_sm100.cu).
+// Parameters of one CTA-pair implicit-GEMM launch (conv_gemm_sm100.cu).  K is processed in 64-channel
+// blocks.  A "group" is one A box (a_rows rows x 64 channels) together with the G weight tiles of the
+// taps that read it (G = 3: the kw taps of one kh of a 3x3/stride-1 layer; G = 1 otherwise).
 struct ConvGemmParams {
   int P;                 // output rows to compute: batch * (H+2) * (W+2)
-  int num_m_tiles;       // ceil(P / 128)
-  int num_n_tiles;       // ceil(Cout_padded / BN)
-  int n_taps;            // 1 or 9
-  int kb_per_tap;        // Cin_padded / BK
-  int a_row_off[9];      // row offset of tap t in the A matrix
-  int BN, BK;            // tile sizes (BK 64 -> 128B swizzle, 32 -> 64B swizzle)
+  int num_m_tiles;       // ceil(P / 256): one tile per CTA pair
+  int num_n_tiles;       // Cout_padded / BN
+  int n_groups;          // A boxes per k-block
+  int kb_per_tap;        // ceil(Cin / 64)
+  int a_row_off[9];      // row offset of group g's A box
+  int b_tap0[9];         // first weight tap of group g (K layout is tap-major)
+  int a_rows;            // rows of the A box (128, or 130 with tap reuse)
+  int BN;                // N of the pair tile (each CTA loads BN/2 weight rows)
   int num_stages;
+  int nbuf;              // epilogue staging buffers per warp (1 or 2)
   int Hp, Wp;            // padded output size (halo test)
-  int out_pitch;         // elements
-  void* out;             // 16-bit output rows (channel offset already applied)
   const float* bias;     // [num_n_tiles*BN]
-  const void* residual;  // 16-bit rows or nullptr
-  int res_pitch;
+  int has_res;           // residual tile added after the activation (shortcut fused)
   int leaky;
-  int is_fp16;
+  int dbg;               // ablation bits (AY_DBG): 1 no MMA, 2 no operand TMA, 4 no output store, 8 no residual
   // fused YOLO decode (head convolutions)
   int head;
   float* dec_out;        // [B, dec_rows_total, dec_cols]
@@ -66,48 +68,11 @@ struct ConvGemmParams {
   float anchor_w[8], anchor_h[8];   // already divided by stride (models.py:122)
   unsigned int* err_flag;
 };
-
-int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p,
-                     int num_sms, cudaStream_t stream);
-int conv_gemm_smem_bytes(int BN, int BK, int stages);
-int conv_gemm_pick_stages(int BN, int BK);
-
-// Parameters of one CTA-pair implicit-GEMM launch (conv_gemm2_sm100.cu).  A "group" is one A box
-// (a_rows rows x BK channels) together with the G weight tiles of the taps that read it.
-struct ConvGemm2Params {
-  int P;                 // output rows to compute: batch * (H+2) * (W+2)
-  int num_m_tiles;       // ceil(P / 256): one tile per CTA pair
-  int num_n_tiles;       // Cout_padded / BN
-  int n_groups;          // A boxes per k-block (3x3 s1 with tap reuse: 3; otherwise = number of taps)
-  int G;                 // taps per group (3 with reuse, else 1)
-  int kb_per_tap;        // Cin_padded / BK
-  int a_row_off[9];      // row offset of group g's A box
-  int a_rows;            // rows of the A box (128, or 130 with reuse)
-  int BN, BK;            // BN: N of the pair tile (each CTA loads BN/2 weight rows)
-  int num_stages;
-  int base_off_mode;     // 1: descriptor base offset = rows skipped (PTX rule); 0: always 0
-  int b_swap;            // debug: swap which CTA loads which half of the weight tile
-  int dbg;               // ablation bits (AY_DBG): 1 no MMA, 2 no operand TMA, 4 no output store, 8 no residual
-  int Hp, Wp;            // padded output size (halo test)
-  int out_pitch;
-  void* out;
-  const float* bias;
-  const void* residual;
-  int res_pitch;
-  int leaky;
-  int is_fp16;
-  int head;
-  float* dec_out;
-  int dec_rows_total, dec_row_off, dec_cols, n_anchors, cout;
-  float stride;
-  float anchor_w[8], anchor_h[8];
-  unsigned int* err_flag;
-};
-int launch_conv_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut,
-                      const CUtensorMap& tmRes, const CUtensorMap& tmResPF, const ConvGemm2Params& p, int num_sms,
-                      cudaStream_t stream);
-int conv_gemm2_stage_bytes(int BN, int BK, int G, int a_rows);
-int conv_gemm2_pick_stages(int BN, int BK, int G, int a_rows);
+int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
+                     const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
+                     cudaStream_t stream);
+int conv_gemm_stage_bytes(int BN, int G, int a_rows);
+void conv_gemm_pick_smem(int BN, int G, int a_rows, int* stages, int* nbuf);
 
 // aux_kernels.cu ------------------------------------------------------------
 struct FirstConvParams {
@@ -131,8 +96,8 @@ int launch_copy_channels(const void* in, int in_pitch, int Cp, long long rows, v
 int launch_dump_nchw(const void* in, int in_pitch, int C, int batch, int H, int W, int is_fp16,
                      float* out, cudaStream_t s);
 struct RefConvParams {
-  const void* in; int in_pitch; int Cin_p; int H, W;          // input (unpadded H,W)
-  const void* w; int ktot;                                     // [Cout_p][taps*Cin_p] 16-bit
+  const void* in; int in_pitch; int Cin_p; int Cin_k; int H, W;   // input (unpadded H,W); Cin_k: weight columns per tap
+  const void* w; int ktot;                                     // [Cout_p][taps*Cin_k] 16-bit
   const float* bias; int cout_p; int size, stride; int leaky;
   const void* residual; int res_pitch;
   void* out; int out_pitch; int Ho, Wo; int batch; int is_fp16;

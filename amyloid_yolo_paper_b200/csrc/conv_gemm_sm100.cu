@@ -1,27 +1,37 @@
-// Implicit-GEMM convolution for sm_100a: TMA -> shared memory -> tcgen05.mma -> TMEM
-// -> fused epilogue (bias, LeakyReLU, residual add, halo zeroing, 16-bit store, or
-// the YOLO decode for head convolutions).
+// Implicit-GEMM convolution for sm_100a, CTA-pair version:
+//   TMA -> shared memory -> tcgen05.mma.cta_group::2 (UMMA 256 x BN x 16) -> TMEM -> fused epilogue.
 //
 // Replaces, for the whole network, the reference's per-block
 //   nn.Conv2d + nn.BatchNorm2d + nn.LeakyReLU            (models.py:26-45)
 //   shortcut add                                         (models.py:246-248)
 //   YOLOLayer inference decode                           (models.py:137-169)
 //
-// Formulation.  Activations are zero-haloed NHWC rows (ay_common.h).  For output
-// row m (a padded pixel) and filter tap t, the input row is m + a_row_off[t]; so
-//   out[m, n] = epi( sum_t sum_c A[m + a_row_off[t], c] * W[n, t*Cin + c] )
-// which is a GEMM whose A tile for k-block (t, c0) is the 128 x BK box of the
-// activation matrix at (row m0 + a_row_off[t], column c0): one 2-D TMA load, the
-// hardware zero-filling rows outside the tensor.  Halo rows of the output are
-// computed like any other row and overwritten with zeros in the epilogue, which
-// keeps the invariant the next layer relies on.
+// Formulation (see ay_common.h): activations are zero-haloed NHWC rows, so for output
+// row m and filter tap t the input row is m + a_row_off[t] and the convolution is
+//   out[m, n] = epi( sum_t sum_c A[m + a_row_off[t], c] * W[n, t*Cin + c] ).
 //
-// Kernel shape: persistent, one CTA per SM, 192 threads:
-//   warp 0   : TMA producer (one lane)           full/empty mbarrier ring, `stages` deep
-//   warp 1   : tcgen05.mma issuer (one lane)     UMMA 128 x BN x 16, fp32 accumulate in TMEM
-//   warps 2-5: epilogue, one TMEM lane quarter each (tcgen05.ld 32x32b.x32)
-// TMEM holds two BN-column accumulators so the epilogue of tile i overlaps the
-// main loop of tile i+1.
+// Why a CTA pair: with one CTA per 128 x 256 tile every 64-channel k-block moves 48 KB
+// from L2 into shared memory for 512 tensor-pipe cycles (94 B/clk/SM, x148 SMs = twice what
+// the L2 fabric delivers) and the MMA reads A and B out of the same shared memory the TMA is
+// filling.  Here two CTAs of a cluster own one 256 x BN tile: each loads its own 128 rows of A
+// and HALF of the weight tile, and the leader CTA issues cta_group::2 MMAs that read both halves.
+//
+// Tap reuse: for a 3x3/stride-1 layer the three kw taps of one kh are the same A rows shifted
+// by one row.  One TMA box of 130 rows serves all three: the MMA descriptor of tap kw starts kw
+// rows (kw*128 B) into the box (the 128-byte swizzle is a function of the absolute shared-memory
+// address, so a row-shifted start address reads the right data).  Per (kh, 64-channel block) a CTA
+// loads 130 rows of A once and three half weight tiles, instead of three full A and weight tiles.
+// K is always processed in 64-channel blocks; a 32-channel input is read through a 64-wide TMA box
+// whose upper half is out of bounds and therefore zero-filled by the hardware.
+//
+// Kernel shape: persistent, one CTA per SM, clusters of 2, 320 threads per CTA:
+//   warp 0   : TMA producer (one lane, in both CTAs; all loads signal the LEADER's full barrier)
+//   warp 1   : tcgen05.mma issuer (one lane, leader CTA only); tcgen05.commit multicast to both CTAs
+//   warps 2-9: epilogue, two warps per TMEM lane quarter (tcgen05.ld 32x32b.x32), alternating 32-column
+//              chunks, so that every scheduler has two epilogue warps to hide each other's latencies
+// TMEM holds two BN-column accumulators so the epilogue of tile i overlaps the main loop of i+1.
+// All global traffic of the epilogue goes through the TMA (residual tile in, result tile out): a
+// thread-per-row ld/st.global touches 32 lines per warp instruction and serialises in the LSU.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -30,27 +40,40 @@
 namespace ay {
 namespace {
 
-constexpr int kBlockM = 128;
-constexpr int kThreads = 192;
-constexpr unsigned long long kSpinLimitCycles = 6000000000ull;  // ~3 s: trap instead of hanging the GPU
+constexpr int kRowsPerCta = 128;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads2 = 32 * (2 + kEpiWarps);   // producer, MMA issuer, 8 epilogue warps
+constexpr unsigned long long kSpinLimit = 6000000000ull;  // ~3 s: trap instead of hanging the GPU
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+__device__ __forceinline__ uint32_t smem_addr(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void bar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
-
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+__device__ __forceinline__ void bar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+__device__ __forceinline__ void bar_arrive_remote(uint32_t cluster_bar) {
+  // default semantics (release at CTA scope): a .release.cluster here compiles to MEMBAR.ALL.GPU + ERRBAR,
+  // which cost 16 % of all stall samples; the TMEM hand-over only needs tcgen05.fence::before_thread_sync
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
-
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned int* err_flag) {
+__device__ __forceinline__ void bar_wait(uint32_t bar, uint32_t parity, unsigned int* err_flag, uint32_t code) {
   uint32_t done = 0;
   unsigned long long t0 = 0;
   uint32_t spins = 0;
@@ -66,39 +89,40 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigne
     if ((++spins & 0xFFF) == 0) {
       unsigned long long now = clock64();
       if (t0 == 0) t0 = now;
-      if (now - t0 > kSpinLimitCycles) {
-        if (err_flag) atomicExch(err_flag, 0xDEAD0001u);
+      if (now - t0 > kSpinLimit) {
+        if (err_flag) atomicExch(err_flag, 0xDEAD0100u | code);
         __trap();
       }
     }
   }
 }
-
-__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint32_t bar, uint32_t dst, int c0, int c1) {
+// 2-D tiled TMA load issued by either CTA of the pair; completion bytes go to `cluster_bar`
+// (an mbarrier of the leader CTA, shared::cluster address).
+__device__ __forceinline__ void tma_load_pair(const CUtensorMap* map, uint32_t cluster_bar, uint32_t dst, int c0, int c1) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(cluster_bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void umma_bf16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                             uint32_t accumulate) {
+__device__ __forceinline__ void umma2_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
       : "memory");
 }
-
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+// arrive on the mbarrier at the same shared-memory offset in both CTAs once all prior MMAs retire
+__device__ __forceinline__ void umma2_commit(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"((uint16_t)3)
+      : "memory");
 }
-
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_load32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -112,146 +136,227 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// K-major operand tile in shared memory, rows of BK 16-bit elements, hardware
-// swizzle equal to the row size (128 B for BK=64, 64 B for BK=32); 8-row groups
-// are contiguous (SBO = 8 * row bytes).  sm_100 descriptor version 1.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t row_bytes) {
-  const uint64_t layout = (row_bytes == 128) ? 2ull : 4ull;  // SWIZZLE_128B : SWIZZLE_64B
-  const uint64_t sbo = (8u * row_bytes) >> 4;
-  return (uint64_t)((saddr >> 4) & 0x3FFFu) | (sbo << 32) | (1ull << 46) | (layout << 61);
-}
-
-__device__ __forceinline__ uint32_t pack2(float lo, float hi, int is_fp16) {
-  if (is_fp16) {
+template <bool FP16>
+__device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
+  if (FP16) {
     __half2 h = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&h);
   }
   __nv_bfloat162 b = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&b);
 }
-
-__device__ __forceinline__ float2 unpack2(uint32_t w, int is_fp16) {
-  if (is_fp16) return __half22float2(*reinterpret_cast<__half2*>(&w));
+template <bool FP16>
+__device__ __forceinline__ float2 unpack_pair(uint32_t w) {
+  if (FP16) return __half22float2(*reinterpret_cast<__half2*>(&w));
   return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
 }
+__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 
-__device__ __forceinline__ float sigmoidf_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+// ---- epilogue staging: 32 rows x 32 channels (64-byte rows, TMA SWIZZLE_64B layout), nbuf (1|2) buffers per warp ----
+constexpr uint32_t kStageBufBytes = 32 * 64;
+constexpr int kMaxStageBufs = 2;
+constexpr int kBiasFloats = 1024;
+constexpr int kBK = 64;                 // channels per k-block: one 128-byte swizzle row
+constexpr uint32_t kRowBytes = 128;
 
-__global__ void __launch_bounds__(kThreads, 1)
+__device__ __forceinline__ void tma_load_local(const CUtensorMap* map, uint32_t bar, uint32_t dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_prefetch_l2(const CUtensorMap* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1)
+               : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void lds128(uint32_t addr, uint4& v) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// G = taps per pipeline stage (3: the kw taps of one kh share one 130-row A box; 1: one tap per stage)
+template <int G, bool FP16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ ConvGemmParams p) {
+                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes,
+                 const __grid_constant__ CUtensorMap tmResPF, const __grid_constant__ ConvGemmParams p) {
+  // shared memory: [S pipeline stages][epilogue staging][mbarriers][tmem slot][bias]
   extern __shared__ uint8_t smem_raw[];
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t a_bytes = kBlockM * p.BK * 2;
-  const uint32_t b_bytes = p.BN * p.BK * 2;
-  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t smem_base = (smem_addr(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_region = (uint32_t)((p.a_rows + 7) & ~7) * kRowBytes;    // multiple of 1024
+  const uint32_t b_tile = (uint32_t)(p.BN / 2) * kRowBytes;
+  const uint32_t stage_bytes = a_region + G * b_tile;
+  const uint32_t tx_bytes = (uint32_t)p.a_rows * kRowBytes + G * b_tile;    // what one CTA's TMA loads deliver
   const int S = p.num_stages;
-  const uint32_t bar_base = smem_base + S * stage_bytes;
-  // barrier i at bar_base + 8*i : full[S], empty[S], tmem_full[2], tmem_empty[2]; then tmem ptr
+  const int nbuf = p.nbuf;
+  const uint32_t staging_base = smem_base + S * stage_bytes;
+  const uint32_t bar_base = staging_base + (uint32_t)(kEpiWarps * nbuf) * kStageBufBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * S + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * S + 4);
+  auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * S + 4 + w * kMaxStageBufs + b); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * S + 4 + kEpiWarps * kMaxStageBufs);
+  // whole-layer bias staged once: with this much shared memory the L1 is ~1 KB, so a global bias load
+  // would be an L2 round trip in the middle of the epilogue's dependency chain
+  float* s_bias = reinterpret_cast<float*>(smem_raw + (tmem_slot - smem_addr(smem_raw)) + 16u);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_rank();
+  const bool leader = rank == 0;
   const uint32_t tmem_cols = (p.BN <= 16) ? 32u : (p.BN <= 32) ? 64u : (p.BN <= 64) ? 128u : (p.BN <= 128) ? 256u : 512u;
+  const bool has_res = p.has_res && !(p.dbg & 8);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmOut)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmRes)) : "memory");
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), 1);
+      bar_init(full_bar(s), 1);     // leader's copy is the one in use: 1 arrive.expect_tx + bytes of both CTAs
+      bar_init(empty_bar(s), 1);    // tcgen05.commit multicast
     }
     for (int a = 0; a < 2; ++a) {
-      mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 128);
+      bar_init(tfull_bar(a), 1);                // tcgen05.commit multicast
+      bar_init(tempty_bar(a), 2 * kEpiWarps);   // leader's copy: 8 epilogue warps x 2 CTAs
     }
+    for (int w = 0; w < kEpiWarps; ++w)
+      for (int b = 0; b < kMaxStageBufs; ++b) bar_init(res_bar(w, b), 1);   // residual TMA loads, per epilogue warp
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols)
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols)
                  : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
   }
-  tcgen05_fence_before();
+  for (int i = threadIdx.x; i < p.num_n_tiles * p.BN; i += kThreads2) s_bias[i] = __ldg(p.bias + i);
   __syncthreads();
-  tcgen05_fence_after();
+  fence_before();
+  cluster_sync_all();
+  fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
   const int total_tiles = p.num_m_tiles * p.num_n_tiles;
-  const int k_iters = p.n_taps * p.kb_per_tap;
+  const int n_clusters = gridDim.x >> 1;
+  const int first_tile = blockIdx.x >> 1;
+  const int units = p.n_groups * p.kb_per_tap;      // pipeline stages consumed per tile
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m0 = (tile / p.num_n_tiles) * kBlockM;
-        const int n0 = (tile % p.num_n_tiles) * p.BN;
-        for (int t = 0; t < p.n_taps; ++t) {
-          const int arow = m0 + p.a_row_off[t];
+      // The residual tile (128 rows x BN channels of this CTA) is pulled into L2 one tile ahead: the epilogue's
+      // small TMA loads then see L2 latency instead of HBM latency, with no shared-memory cost for the bytes in flight.
+      if (has_res && first_tile < total_tiles)
+        tma_prefetch_l2(&tmResPF, (first_tile % p.num_n_tiles) * p.BN,
+                        (first_tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta);
+      for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+        const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
+        const int n0 = (tile % p.num_n_tiles) * p.BN + (int)rank * (p.BN / 2);
+        if (has_res && tile + n_clusters < total_tiles) {
+          const int nt = tile + n_clusters;
+          tma_prefetch_l2(&tmResPF, (nt % p.num_n_tiles) * p.BN, (nt / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta);
+        }
+        for (int g = 0; g < p.n_groups; ++g) {
+          const int arow = m0 + p.a_row_off[g];
+          const int bcol0 = p.b_tap0[g] * p.kb_per_tap * kBK;
           for (int kb = 0; kb < p.kb_per_tap; ++kb) {
-            mbar_wait(empty_bar(stage), phase ^ 1u, p.err_flag);
-            mbar_expect_tx(full_bar(stage), stage_bytes);
-            const uint32_t sa = smem_base + stage * stage_bytes;
-            tma_load_2d(&tmA, full_bar(stage), sa, kb * p.BK, arow);
-            tma_load_2d(&tmB, full_bar(stage), sa + a_bytes, (t * p.kb_per_tap + kb) * p.BK, n0);
+            bar_wait(empty_bar(stage), phase ^ 1u, p.err_flag, 1);
+            const uint32_t lead_full = map_to_cta(full_bar(stage), 0);
+            if (p.dbg & 2) {                                   // ablation: no operand loads
+              if (leader) bar_expect_tx(full_bar(stage), 0u);
+            } else {
+              if (leader) bar_expect_tx(full_bar(stage), 2u * tx_bytes);
+              const uint32_t sa = smem_base + stage * stage_bytes;
+              tma_load_pair(&tmA, lead_full, sa, kb * kBK, arow);
+#pragma unroll
+              for (int j = 0; j < G; ++j)
+                tma_load_pair(&tmB, lead_full, sa + a_region + j * b_tile, bcol0 + (j * p.kb_per_tap + kb) * kBK, n0);
+            }
             if (++stage == S) { stage = 0; phase ^= 1u; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // instruction descriptor: D=f32, A/B = bf16|f16, both K-major, N = BN, M = 128
-      const uint32_t fmt = p.is_fp16 ? 0u : 1u;
+    if (leader && lane == 0) {
+      // instruction descriptor: D=f32, A/B = bf16|f16, both K-major, N = BN, M = 256 (pair)
+      constexpr uint32_t fmt = FP16 ? 0u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(p.BN >> 3) << 17) |
-                             ((uint32_t)(kBlockM >> 4) << 24);
-      const uint32_t row_bytes = p.BK * 2;
+                             ((uint32_t)((2 * kRowsPerCta) >> 4) << 24);
+      // descriptor constants: SWIZZLE_128B (2 << 61), version 1 (1 << 46), SBO = 1024 B (64 << 32).  Tap j of a group
+      // starts j rows (j*128 B) into the A box: the swizzle is a function of the absolute shared-memory address, so
+      // the base-offset field stays 0 (measured on B200: setting it to j gives wrong results).
+      constexpr uint64_t desc_hi = (2ull << 61) | (1ull << 46) | (64ull << 32);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        mbar_wait(tempty_bar(acc), acc_phase ^ 1u, p.err_flag);
-        tcgen05_fence_after();
+      for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+        bar_wait(tempty_bar(acc), acc_phase ^ 1u, p.err_flag, 2);
+        fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.BN);
-        for (int it = 0; it < k_iters; ++it) {
-          mbar_wait(full_bar(stage), phase, p.err_flag);
-          tcgen05_fence_after();
+        for (int it = 0; it < units; ++it) {
+          bar_wait(full_bar(stage), phase, p.err_flag, 3);
+          fence_after();
           const uint32_t sa = smem_base + stage * stage_bytes;
-          const uint64_t adesc = make_smem_desc(sa, row_bytes);
-          const uint64_t bdesc = make_smem_desc(sa + a_bytes, row_bytes);
-          const int ksteps = p.BK >> 4;
-          for (int k = 0; k < ksteps; ++k) {
-            // advance 16 elements (32 bytes) along K inside the swizzle row: +2 in 16-byte units
-            umma_bf16_ss(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                         (uint32_t)((it | k) != 0));
+          const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFFu);
+          const uint64_t b0 = desc_hi | (uint64_t)(((sa + a_region) >> 4) & 0x3FFFu);
+          if (!(p.dbg & 1)) {
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+#pragma unroll
+              for (int k = 0; k < kBK / 16; ++k)
+                umma2_f16(d_tmem, a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k), b0 + (uint64_t)(j * (b_tile >> 4) + 2 * k), idesc,
+                          (uint32_t)((it | j | k) != 0));
+            }
           }
-          umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
+          umma2_commit(empty_bar(stage));   // frees this stage in both CTAs
           if (++stage == S) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+        umma2_commit(tfull_bar(acc));       // accumulator complete -> both epilogues
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
   } else {
-    // ---------------- epilogue: warps 2..5, TMEM lane quarter = warp % 4 ----------------
+    // ---------------- epilogue: warps 2..9; TMEM lane quarter = warp % 4, chunk parity = (warp-2)/4 ----------------
+    const int ew = warp - 2;
     const int quarter = warp & 3;
+    const int half = ew >> 2;
     const int row_in_tile = quarter * 32 + lane;
     const uint32_t lane_addr = ((uint32_t)(quarter * 32)) << 16;
+    const uint32_t stg = staging_base + (uint32_t)(ew * nbuf) * kStageBufBytes;
+    const uint32_t my_row = (uint32_t)lane * 64u;
+    const uint32_t my_xor = ((uint32_t)lane >> 1) & 3u;          // SWIZZLE_64B: 16-byte chunk ^= (row / 2) % 4
     const int hw = p.Hp * p.Wp;
+    const int nchunks = p.BN >> 5;
+    uint32_t cid = 0;                                            // chunks processed by this warp -> buffer and barrier phase
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int m0 = (tile / p.num_n_tiles) * kBlockM;
+    auto wait_buffer_free = [&]() {      // all but the newest (nbuf-1) bulk stores of this thread have read their buffer
+      if (nbuf == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
+    };
+    for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+      const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
       const int n0 = (tile % p.num_n_tiles) * p.BN;
+      const int row0 = m0 + quarter * 32;                        // first of this warp's 32 rows
       const int m = m0 + row_in_tile;
       const bool in_range = m < p.P;
       const int img = m / hw;
@@ -259,120 +364,175 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int yy = pix / p.Wp;
       const int xx = pix - yy * p.Wp;
       const bool halo = (yy == 0) | (yy == p.Hp - 1) | (xx == 0) | (xx == p.Wp - 1);
+      const bool zero_row = halo | !in_range;
 
-      mbar_wait(tfull_bar(acc), acc_phase, p.err_flag);
-      tcgen05_fence_after();
-      const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
-
-      for (int c0 = 0; c0 < p.BN; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(t_acc + (uint32_t)c0, v);
-        const int nbase = n0 + c0;
-        if (!p.head) {
-          const float4* bias4 = reinterpret_cast<const float4*>(p.bias + nbase);
-          uint32_t packed[16];
-          uint4 res[4];
-          const bool use_res = (p.residual != nullptr) && in_range && !halo;
-          if (use_res) {
-            const uint4* rp = reinterpret_cast<const uint4*>(
-                static_cast<const uint16_t*>(p.residual) + (size_t)m * p.res_pitch + nbase);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) res[q] = __ldg(rp + q);
-          }
+      if (!p.head) {
+        if (has_res && half < nchunks && lane == 0) {            // residual of my first chunk, before the MMAs finish
+          wait_buffer_free();
+          const uint32_t b = cid % nbuf;
+          bar_expect_tx(res_bar(ew, b), kStageBufBytes);
+          tma_load_local(&tmRes, res_bar(ew, b), stg + b * kStageBufBytes, n0 + half * 32, row0);
+        }
+        bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
+        fence_after();
+        const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
+        for (int c = half; c < nchunks; c += 2, ++cid) {
+          const uint32_t b = cid % nbuf;
+          const uint32_t buf = stg + b * kStageBufBytes;
+          uint32_t v[32];
+          tmem_load32(t_acc + (uint32_t)(c * 32), v);
+          // bias + LeakyReLU while the residual is still in flight
+          const float4* bias4 = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
+          float f[32];
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
-            const float4 b = __ldg(bias4 + q);
-            float f0 = __uint_as_float(v[4 * q + 0]) + b.x;
-            float f1 = __uint_as_float(v[4 * q + 1]) + b.y;
-            float f2 = __uint_as_float(v[4 * q + 2]) + b.z;
-            float f3 = __uint_as_float(v[4 * q + 3]) + b.w;
-            if (p.leaky) {
-              f0 = f0 > 0.f ? f0 : 0.1f * f0;
-              f1 = f1 > 0.f ? f1 : 0.1f * f1;
-              f2 = f2 > 0.f ? f2 : 0.1f * f2;
-              f3 = f3 > 0.f ? f3 : 0.1f * f3;
-            }
-            if (use_res) {
-              const uint32_t* rw = reinterpret_cast<const uint32_t*>(&res[q >> 1]);
-              const float2 r01 = unpack2(rw[(q & 1) * 2 + 0], p.is_fp16);
-              const float2 r23 = unpack2(rw[(q & 1) * 2 + 1], p.is_fp16);
-              f0 += r01.x; f1 += r01.y; f2 += r23.x; f3 += r23.y;
-            }
-            if (halo) { f0 = f1 = f2 = f3 = 0.f; }
-            packed[2 * q + 0] = pack2(f0, f1, p.is_fp16);
-            packed[2 * q + 1] = pack2(f2, f3, p.is_fp16);
+            const float4 bb = bias4[q];
+            f[4 * q + 0] = __uint_as_float(v[4 * q + 0]) + bb.x;
+            f[4 * q + 1] = __uint_as_float(v[4 * q + 1]) + bb.y;
+            f[4 * q + 2] = __uint_as_float(v[4 * q + 2]) + bb.z;
+            f[4 * q + 3] = __uint_as_float(v[4 * q + 3]) + bb.w;
           }
-          if (in_range) {
-            uint4* op = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out) + (size_t)m * p.out_pitch + nbase);
+          if (p.leaky) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-              op[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+            for (int e = 0; e < 32; ++e) f[e] = fmaxf(f[e], 0.1f * f[e]);   // == (x > 0 ? x : 0.1x) for every x
           }
-        } else if (in_range && !halo) {
-          // fused YOLOLayer decode (models.py:137-169): channel ch = a*(5+C) + f
-          const int G = p.Wp - 2;
-          const int gx = xx - 1, gy = yy - 1;
-          float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols;
-#pragma unroll 1
+          if (has_res) {
+            bar_wait(res_bar(ew, b), (cid / nbuf) & 1u, p.err_flag, 5);
+          } else {
+            if (lane == 0) wait_buffer_free();
+            __syncwarp();
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {                          // 8 channels = one 16-byte chunk of my row
+            const uint32_t addr = buf + my_row + (((uint32_t)q ^ my_xor) << 4);
+            if (has_res) {
+              uint4 r;
+              lds128(addr, r);
+              const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 rr = unpack_pair<FP16>(rw[e]);
+                f[8 * q + 2 * e] += rr.x;
+                f[8 * q + 2 * e + 1] += rr.y;
+              }
+            }
+            uint4 o;
+            o.x = pack_pair<FP16>(f[8 * q + 0], f[8 * q + 1]);
+            o.y = pack_pair<FP16>(f[8 * q + 2], f[8 * q + 3]);
+            o.z = pack_pair<FP16>(f[8 * q + 4], f[8 * q + 5]);
+            o.w = pack_pair<FP16>(f[8 * q + 6], f[8 * q + 7]);
+            if (zero_row) o = make_uint4(0u, 0u, 0u, 0u);
+            sts128(addr, o);
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) {
+            if (!(p.dbg & 4)) tma_store_2d(&tmOut, buf, n0 + c * 32, row0);
+            if (has_res && c + 2 < nchunks) {                    // residual of my next chunk
+              wait_buffer_free();
+              const uint32_t b1 = (cid + 1) % nbuf;
+              bar_expect_tx(res_bar(ew, b1), kStageBufBytes);
+              tma_load_local(&tmRes, res_bar(ew, b1), stg + b1 * kStageBufBytes, n0 + (c + 2) * 32, row0);
+            }
+          }
+        }
+      } else {
+        // fused YOLOLayer decode (models.py:137-169): channel ch = a*(5+C) + f
+        bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
+        fence_after();
+        const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
+        const int Gd = p.Wp - 2;
+        const int gx = xx - 1, gy = yy - 1;
+        float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols +
+                       ((size_t)gy * Gd + gx) * p.dec_cols;
+        const size_t a_step = (size_t)Gd * Gd * p.dec_cols;
+        for (int c = half; c < nchunks; c += 2) {
+          uint32_t v[32];
+          tmem_load32(t_acc + (uint32_t)(c * 32), v);
+          const int ch0 = n0 + c * 32;
+          int a = ch0 / p.dec_cols, fi = ch0 - a * p.dec_cols;   // running (anchor, field) of channel ch
+#pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int ch = nbase + j;
-            if (ch >= p.cout) break;
-            const int a = ch / p.dec_cols;
-            const int f = ch - a * p.dec_cols;
-            const float t = __uint_as_float(v[j]) + __ldg(p.bias + ch);
-            float r;
-            if (f == 0) r = __fmul_rn(__fadd_rn(sigmoidf_acc(t), (float)gx), p.stride);
-            else if (f == 1) r = __fmul_rn(__fadd_rn(sigmoidf_acc(t), (float)gy), p.stride);
-            else if (f == 2) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_w[a]), p.stride);
-            else if (f == 3) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_h[a]), p.stride);
-            else r = sigmoidf_acc(t);
-            obase[((size_t)a * G * G + (size_t)gy * G + gx) * p.dec_cols + f] = r;
+            const int ch = ch0 + j;
+            if (ch < p.cout && in_range && !halo) {
+              const float t = __uint_as_float(v[j]) + s_bias[ch];
+              float r;
+              if (fi == 0) r = __fmul_rn(__fadd_rn(sigmoid_acc(t), (float)gx), p.stride);
+              else if (fi == 1) r = __fmul_rn(__fadd_rn(sigmoid_acc(t), (float)gy), p.stride);
+              else if (fi == 2) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_w[a]), p.stride);
+              else if (fi == 3) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_h[a]), p.stride);
+              else r = sigmoid_acc(t);
+              obase[(size_t)a * a_step + fi] = r;
+            }
+            if (++fi == p.dec_cols) { fi = 0; ++a; }
           }
         }
       }
-      tcgen05_fence_before();
-      mbar_arrive(tempty_bar(acc));
+      // this warp is done reading the accumulator: one arrival per warp on the LEADER's barrier
+      fence_before();
+      __syncwarp();
+      if (lane == 0) bar_arrive_remote(map_to_cta(tempty_bar(acc), 0));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores have left shared memory and landed
   }
 
-  tcgen05_fence_before();
-  __syncthreads();
+  // both CTAs must stay resident until the pair's last MMA, commit and remote arrive have landed
+  fence_before();
+  cluster_sync_all();
   if (warp == 2) {
-    tcgen05_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+    fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
 }
 
 }  // namespace
 
-int conv_gemm_smem_bytes(int BN, int BK, int stages) {
-  return stages * (kBlockM * BK * 2 + BN * BK * 2) + 8 * (2 * stages + 4) + 16 + 1024;
+int conv_gemm_stage_bytes(int BN, int G, int a_rows) {
+  return ((a_rows + 7) & ~7) * (int)kRowBytes + G * (BN / 2) * (int)kRowBytes;
 }
 
-int conv_gemm_pick_stages(int BN, int BK) {
-  const int stage = kBlockM * BK * 2 + BN * BK * 2;
-  int s = (200 * 1024) / stage;
+static int conv_gemm_fixed_smem(int num_stages, int nbuf) {
+  return kEpiWarps * nbuf * (int)kStageBufBytes + 8 * (2 * num_stages + 4 + kEpiWarps * kMaxStageBufs) + 16 +
+         4 * kBiasFloats + 1024 /*alignment*/;
+}
+
+// -> stages (2..8) and staging buffers per epilogue warp (2 when they fit beside >= 3 stages, else 1)
+void conv_gemm_pick_smem(int BN, int G, int a_rows, int* stages, int* nbuf) {
+  const int sb = conv_gemm_stage_bytes(BN, G, a_rows);
+  const int limit = 227 * 1024;
+  int nb = 2;
+  int s = (limit - conv_gemm_fixed_smem(8, nb)) / sb;
+  if (s < 3) {
+    nb = 1;
+    s = (limit - conv_gemm_fixed_smem(8, nb)) / sb;
+  }
   if (s > 8) s = 8;
-  if (s < 2) s = 2;
-  return s;
+  *stages = s;
+  *nbuf = nb;
 }
 
-int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p, int num_sms,
+int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
+                     const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
                      cudaStream_t stream) {
-  if (p.BN % 32 != 0 || p.BN < 32 || p.BN > 256 || (p.BK != 32 && p.BK != 64)) {
-    set_error("conv_gemm: unsupported tile BN=%d BK=%d", p.BN, p.BK);
+  if (p.BN % 32 != 0 || p.BN < 32 || p.BN > 256 || p.num_stages < 2 || p.num_stages > 8 || (G != 1 && G != 3) ||
+      (p.nbuf != 1 && p.nbuf != 2) || p.num_n_tiles * p.BN > kBiasFloats) {
+    set_error("conv_gemm: unsupported tile BN=%d G=%d stages=%d nbuf=%d n_tiles=%d", p.BN, G, p.num_stages, p.nbuf,
+              p.num_n_tiles);
     return AY_EINVAL;
   }
-  static int configured_smem = 0;
-  const int smem = conv_gemm_smem_bytes(p.BN, p.BK, p.num_stages);
-  if (smem > configured_smem) {
-    AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    configured_smem = 227 * 1024;
-  }
+  const int smem = p.num_stages * conv_gemm_stage_bytes(p.BN, G, p.a_rows) + conv_gemm_fixed_smem(p.num_stages, p.nbuf);
   const int total = p.num_m_tiles * p.num_n_tiles;
-  const int grid = total < num_sms ? total : num_sms;
-  conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(tmA, tmB, p);
+  const int pairs = num_sms / 2;
+  const int grid = 2 * (total < pairs ? total : pairs);
+#define AY_LAUNCH(GG, FF)                                                                                              \
+  do {                                                                                                                 \
+    AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<GG, FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));  \
+    conv_gemm_kernel<GG, FF><<<grid, kThreads2, smem, stream>>>(tmA, tmB, tmOut, tmRes, tmResPF, p);                   \
+  } while (0)
+  if (G == 3) { if (is_fp16) AY_LAUNCH(3, true); else AY_LAUNCH(3, false); }
+  else        { if (is_fp16) AY_LAUNCH(1, true); else AY_LAUNCH(1, false); }
+#undef AY_LAUNCH
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

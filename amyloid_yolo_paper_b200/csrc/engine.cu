@@ -93,7 +93,8 @@ struct Layer {
   ActView out;                      // where the output lives (ptr == nullptr: not materialised)
   bool owns = false;                // this layer allocated out.ptr
   // convolution
-  int cin = 0, cin_p = 0, cout_rows = 0, ktot = 0, BN = 0, BK = 0, stages = 0;
+  int cin = 0, cin_p = 0, cin_k = 0, cout_rows = 0, ktot = 0;   // cin_p: channels stored (x32); cin_k: K per tap (x64)
+  int BN = 0, G = 1, a_rows = 128, stages = 0, nbuf = 1;
   int impl = 0;                     // 0 none, 1 tcgen05 gemm, 2 first-layer direct
   void* w16 = nullptr;              // [cout_rows][ktot] 16-bit (gemm)
   float* w32 = nullptr;             // [cout][27] fp32 (first layer)
@@ -106,10 +107,9 @@ struct Layer {
   void* planes = nullptr;           // stride-2: parity planes [4][plane_rows][cin_p]
   long long plane_rows = 0;
   float* raw_f32 = nullptr;         // reference path scratch for heads
-  CUtensorMap tmA, tmB;
-  // CTA-pair kernel (conv_gemm2_sm100.cu)
-  int G = 1, a_rows = 128, stages2 = 0;
-  CUtensorMap tmA2, tmB2, tmOut, tmRes, tmResPF;   // tmOut/tmRes: 32-channel x 32-row boxes for the epilogue's TMA store / residual load
+  // tmA: a_rows x 64-channel box of the input (or parity planes); tmB: BN/2 x 64 box of the weights;
+  // tmOut/tmRes: 32-row x 32-channel boxes of the epilogue's TMA store / residual load; tmResPF: L2 prefetch box
+  CUtensorMap tmA, tmB, tmOut, tmRes, tmResPF;
   // yolo
   int dec_row_off = 0;
   // route copy fallback
@@ -129,7 +129,7 @@ struct ay_ctx {
   std::vector<ay::Layer> layers;
   int in_channels = 3, img_size = 416, max_batch = 0, is_fp16 = 0;
   bool built = false, finalized = false, use_ref = false;
-  int gemm_version = 2, base_off_mode = 0, b_swap = 0, dbg = 0;   // AY_GEMM_V / AY_BASE_OFF / AY_B_SWAP (debug overrides)
+  int dbg = 0;                        // AY_DBG ablation bits (see ConvGemmParams::dbg)
   int dec_rows = 0, dec_cols = 0;
   int* idx_y = nullptr;               // nearest-resize tables (device), rebuilt when the source size changes
   int* idx_x = nullptr;
@@ -233,9 +233,6 @@ extern "C" int ay_create(ay_ctx** out, int device) {
     return AY_ENOMEM;
   }
   cudaMemset(ctx->err_flag, 0, sizeof(unsigned int));
-  if (const char* e = getenv("AY_GEMM_V")) ctx->gemm_version = atoi(e) == 1 ? 1 : 2;
-  if (const char* e = getenv("AY_BASE_OFF")) ctx->base_off_mode = atoi(e) != 0;
-  if (const char* e = getenv("AY_B_SWAP")) ctx->b_swap = atoi(e) != 0;
   if (const char* e = getenv("AY_DBG")) ctx->dbg = atoi(e);
   *out = ctx;
   return AY_OK;
@@ -457,28 +454,27 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     if (!in.ptr) { set_error("layer %d: input of the convolution is not materialised", i); return AY_EINVAL; }
     const int taps = L.d.size * L.d.size;
     L.cin_p = in.Cp;
-    L.ktot = taps * L.cin_p;
-    L.BK = (L.cin_p % 64 == 0) ? 64 : 32;
+    L.cin_k = ay::round_up(L.cin_p, 64);
+    L.ktot = taps * L.cin_k;
     const int cout_p = ay::round_up(L.C, 32);
     if (L.is_head) L.BN = cout_p <= 256 ? cout_p : 256;
     else L.BN = (cout_p % 256 == 0) ? 256 : (cout_p % 128 == 0) ? 128 : (cout_p % 64 == 0) ? 64 : 32;
     L.cout_rows = ay::round_up(cout_p, L.BN);
-    L.stages = ay::conv_gemm_pick_stages(L.BN, L.BK);
+    L.G = (L.d.size == 3 && L.d.stride == 1) ? 3 : 1;
+    L.a_rows = L.G == 3 ? 130 : 128;
+    ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, &L.stages, &L.nbuf);
+    if (L.stages < 2) { set_error("layer %d: tile does not fit in shared memory", i); return AY_EINVAL; }
     AY_TRY(ay::dev_alloc(ctx, &L.w16, (size_t)L.cout_rows * L.ktot * 2, true));
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.cout_rows, true));
-    AY_TRY(ay::make_map_2d(&L.tmB, L.w16, L.ktot, L.cout_rows, L.ktot, L.BK, L.BN, ctx->is_fp16));
-    L.G = (L.d.size == 3 && L.d.stride == 1 && L.BK == 64) ? 3 : 1;
-    L.a_rows = L.G == 3 ? 130 : 128;
-    L.stages2 = ay::conv_gemm2_pick_stages(L.BN, L.BK, L.G, L.a_rows);
-    AY_TRY(ay::make_map_2d(&L.tmB2, L.w16, L.ktot, L.cout_rows, L.ktot, L.BK, L.BN / 2, ctx->is_fp16));
+    AY_TRY(ay::make_map_2d(&L.tmB, L.w16, L.ktot, L.cout_rows, L.ktot, 64, L.BN / 2, ctx->is_fp16));
+    // A boxes are always 64 channels wide; when the tensor stores only 32 (cin_p = 32) the upper half of the
+    // box lies outside the tensor and the TMA zero-fills it (the matching weight columns are zero as well)
     if (L.d.stride == 2) {
       L.plane_rows = ay::padded_rows(max_batch, L.H, L.W);
       AY_TRY(ay::dev_alloc(ctx, &L.planes, (size_t)4 * L.plane_rows * L.cin_p * 2, true));
-      AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, L.BK, 128, ctx->is_fp16));
-      AY_TRY(ay::make_map_2d(&L.tmA2, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, L.BK, L.a_rows, ctx->is_fp16));
+      AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, 64, L.a_rows, ctx->is_fp16));
     } else {
-      AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, L.BK, 128, ctx->is_fp16));
-      AY_TRY(ay::make_map_2d(&L.tmA2, in.ptr, L.cin_p, in.rows_alloc, in.pitch, L.BK, L.a_rows, ctx->is_fp16));
+      AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, 64, L.a_rows, ctx->is_fp16));
     }
     if (!L.is_head) {
       const ActView& tgt = L.fused_shortcut >= 0 ? Ls[L.fused_shortcut].out : L.out;
@@ -487,9 +483,9 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       AY_TRY(ay::make_map_2d(&L.tmRes, rv.ptr, rv.Cp, rv.rows_alloc, rv.pitch, 32, 32, ctx->is_fp16));
       AY_TRY(ay::make_map_2d(&L.tmResPF, rv.ptr, rv.Cp, rv.rows_alloc, rv.pitch, L.BN, 128, ctx->is_fp16, /*swizzle=*/false));
     } else {
-      L.tmOut = L.tmA2;
-      L.tmRes = L.tmA2;
-      L.tmResPF = L.tmA2;
+      L.tmOut = L.tmA;
+      L.tmRes = L.tmA;
+      L.tmResPF = L.tmA;
     }
     if (L.is_head)
       AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.raw_f32),
@@ -522,7 +518,7 @@ extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const flo
     for (int o = 0; o < cout; ++o)
       for (int c = 0; c < cin; ++c)
         for (int t = 0; t < taps; ++t)
-          r[(size_t)o * L.ktot + (size_t)t * L.cin_p + c] = ay::to16(w[((size_t)o * cin + c) * taps + t], ctx->is_fp16);
+          r[(size_t)o * L.ktot + (size_t)t * L.cin_k + c] = ay::to16(w[((size_t)o * cin + c) * taps + t], ctx->is_fp16);
     std::vector<float> b(L.cout_rows, 0.f);
     memcpy(b.data(), bias, sizeof(float) * cout);
     AY_CUDA(cudaMemcpy(L.w16, r.data(), r.size() * 2, cudaMemcpyHostToDevice));
@@ -602,7 +598,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
 
   if (ctx->use_ref) {
     ay::RefConvParams r{};
-    r.in = in.ptr; r.in_pitch = in.pitch; r.Cin_p = L.cin_p; r.H = in.H; r.W = in.W;
+    r.in = in.ptr; r.in_pitch = in.pitch; r.Cin_p = L.cin_p; r.Cin_k = L.cin_k; r.H = in.H; r.W = in.W;
     r.w = L.w16; r.ktot = L.ktot; r.bias = L.bias; r.cout_p = L.is_head ? L.cout_rows : target->Cp;
     r.size = L.d.size; r.stride = L.d.stride; r.leaky = L.d.leaky;
     r.residual = res ? res->ptr : nullptr; r.res_pitch = res ? res->pitch : 0;
@@ -626,103 +622,55 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
     return AY_OK;
   }
 
-  if (ctx->gemm_version == 2) {
-    ay::ConvGemm2Params q{};
-    q.P = (int)ay::padded_rows(batch, L.H, L.W);
-    q.num_m_tiles = (q.P + 255) / 256;
-    q.num_n_tiles = L.cout_rows / L.BN;
-    q.G = L.G;
-    q.a_rows = L.a_rows;
-    q.kb_per_tap = L.cin_p / L.BK;
-    if (L.d.size == 1) {
-      q.n_groups = 1;
-      q.a_row_off[0] = 0;
-    } else if (L.d.stride == 1) {
-      if (L.G == 3) {
-        q.n_groups = 3;
-        for (int kh = 0; kh < 3; ++kh) q.a_row_off[kh] = (kh - 1) * Wq - 1;
-      } else {
-        q.n_groups = 9;
-        for (int kh = 0; kh < 3; ++kh)
-          for (int kw = 0; kw < 3; ++kw) q.a_row_off[kh * 3 + kw] = (kh - 1) * Wq + (kw - 1);
-      }
-    } else {
-      AY_TRY(ay::launch_s2_gather(in.ptr, in.pitch, L.cin_p / 8, batch, in.H, in.W, L.planes, L.plane_rows, st));
-      ++ctx->launches;
-      q.n_groups = 9;
-      for (int kh = 0; kh < 3; ++kh)
-        for (int kw = 0; kw < 3; ++kw) {
-          const long long off = (long long)((kh & 1) * 2 + (kw & 1)) * L.plane_rows + (kh >> 1) * Wq + (kw >> 1);
-          if (off > 0x7fffffffLL - (1LL << 26)) { set_error("layer %d: batch too large for 32-bit row offsets", i); return AY_EINVAL; }
-          q.a_row_off[kh * 3 + kw] = (int)off;
-        }
-    }
-    q.BN = L.BN; q.BK = L.BK; q.num_stages = L.stages2;
-    q.base_off_mode = ctx->base_off_mode; q.b_swap = ctx->b_swap; q.dbg = ctx->dbg;
-    q.Hp = Hq; q.Wp = Wq;
-    q.bias = L.bias; q.leaky = L.d.leaky; q.is_fp16 = ctx->is_fp16;
-    q.err_flag = ctx->err_flag;
-    if (L.is_head) {
-      q.head = 1;
-      q.dec_out = dec_out; q.dec_rows_total = ctx->dec_rows; q.dec_row_off = Y->dec_row_off;
-      q.dec_cols = ctx->dec_cols; q.n_anchors = Y->d.n_anchors; q.cout = L.C;
-      const double stride = (double)ctx->img_size / (double)L.H;   // models.py:119
-      q.stride = (float)stride;
-      for (int a = 0; a < Y->d.n_anchors; ++a) {
-        q.anchor_w[a] = (float)((double)Y->d.anchors[2 * a] / stride);      // models.py:122-124
-        q.anchor_h[a] = (float)((double)Y->d.anchors[2 * a + 1] / stride);
-      }
-    } else {
-      q.out = target->ptr; q.out_pitch = target->pitch;
-      q.residual = res ? res->ptr : nullptr; q.res_pitch = res ? res->pitch : 0;
-      q.cout = L.C;
-    }
-    ++ctx->launches;
-    return ay::launch_conv_gemm2(L.tmA2, L.tmB2, L.tmOut, L.tmRes, L.tmResPF, q, ctx->num_sms, st);
-  }
-
-  ay::ConvGemmParams p{};
-  p.P = (int)ay::padded_rows(batch, L.H, L.W);
-  p.num_m_tiles = (p.P + 127) / 128;
-  p.num_n_tiles = L.cout_rows / L.BN;
-  p.n_taps = L.d.size * L.d.size;
-  p.kb_per_tap = L.cin_p / L.BK;
+  ay::ConvGemmParams q{};
+  q.P = (int)ay::padded_rows(batch, L.H, L.W);
+  q.num_m_tiles = (q.P + 255) / 256;
+  q.num_n_tiles = L.cout_rows / L.BN;
+  q.a_rows = L.a_rows;
+  q.kb_per_tap = L.cin_k / 64;
   if (L.d.size == 1) {
-    p.a_row_off[0] = 0;
+    q.n_groups = 1;
+    q.a_row_off[0] = 0;
+    q.b_tap0[0] = 0;
   } else if (L.d.stride == 1) {
-    for (int kh = 0; kh < 3; ++kh)
-      for (int kw = 0; kw < 3; ++kw) p.a_row_off[kh * 3 + kw] = (kh - 1) * Wq + (kw - 1);
+    q.n_groups = 3;                       // one group per kh: the three kw taps share a 130-row A box
+    for (int kh = 0; kh < 3; ++kh) {
+      q.a_row_off[kh] = (kh - 1) * Wq - 1;
+      q.b_tap0[kh] = kh * 3;
+    }
   } else {
     AY_TRY(ay::launch_s2_gather(in.ptr, in.pitch, L.cin_p / 8, batch, in.H, in.W, L.planes, L.plane_rows, st));
     ++ctx->launches;
+    q.n_groups = 9;
     for (int kh = 0; kh < 3; ++kh)
       for (int kw = 0; kw < 3; ++kw) {
         const long long off = (long long)((kh & 1) * 2 + (kw & 1)) * L.plane_rows + (kh >> 1) * Wq + (kw >> 1);
         if (off > 0x7fffffffLL - (1LL << 26)) { set_error("layer %d: batch too large for 32-bit row offsets", i); return AY_EINVAL; }
-        p.a_row_off[kh * 3 + kw] = (int)off;
+        q.a_row_off[kh * 3 + kw] = (int)off;
+        q.b_tap0[kh * 3 + kw] = kh * 3 + kw;
       }
   }
-  p.BN = L.BN; p.BK = L.BK; p.num_stages = L.stages;
-  p.Hp = Hq; p.Wp = Wq;
-  p.bias = L.bias; p.leaky = L.d.leaky; p.is_fp16 = ctx->is_fp16;
-  p.err_flag = ctx->err_flag;
+  q.BN = L.BN; q.num_stages = L.stages; q.nbuf = L.nbuf;
+  q.dbg = ctx->dbg;
+  q.Hp = Hq; q.Wp = Wq;
+  q.bias = L.bias; q.leaky = L.d.leaky;
+  q.err_flag = ctx->err_flag;
   if (L.is_head) {
-    p.head = 1;
-    p.dec_out = dec_out; p.dec_rows_total = ctx->dec_rows; p.dec_row_off = Y->dec_row_off;
-    p.dec_cols = ctx->dec_cols; p.n_anchors = Y->d.n_anchors; p.cout = L.C;
+    q.head = 1;
+    q.dec_out = dec_out; q.dec_rows_total = ctx->dec_rows; q.dec_row_off = Y->dec_row_off;
+    q.dec_cols = ctx->dec_cols; q.n_anchors = Y->d.n_anchors; q.cout = L.C;
     const double stride = (double)ctx->img_size / (double)L.H;   // models.py:119
-    p.stride = (float)stride;
+    q.stride = (float)stride;
     for (int a = 0; a < Y->d.n_anchors; ++a) {
-      p.anchor_w[a] = (float)((double)Y->d.anchors[2 * a] / stride);      // models.py:122-124
-      p.anchor_h[a] = (float)((double)Y->d.anchors[2 * a + 1] / stride);
+      q.anchor_w[a] = (float)((double)Y->d.anchors[2 * a] / stride);      // models.py:122-124
+      q.anchor_h[a] = (float)((double)Y->d.anchors[2 * a + 1] / stride);
     }
   } else {
-    p.out = target->ptr; p.out_pitch = target->pitch;
-    p.residual = res ? res->ptr : nullptr; p.res_pitch = res ? res->pitch : 0;
-    p.cout = L.C;
+    q.has_res = res ? 1 : 0;
+    q.cout = L.C;
   }
   ++ctx->launches;
-  return ay::launch_conv_gemm(L.tmA, L.tmB, p, ctx->num_sms, st);
+  return ay::launch_conv_gemm(L.tmA, L.tmB, L.tmOut, L.tmRes, L.tmResPF, q, L.G, ctx->is_fp16, ctx->num_sms, st);
 }
 
 }  // namespace

@@ -9,9 +9,9 @@ def load(path):
     out = []
     for x in csv.DictReader(lines):
         name = x["Kernel Name"]
-        if "_kernel(" not in name or "at::" in name:
+        if "_kernel" not in name or "at::" in name:
             continue
-        short = name.split("(")[0].split("::")[-1]
+        short = name.split("(")[0].split("::")[-1].replace("void ", "")
         out.append((short, x["Grid Size"], float(x["Metric Value"]) / 1e3))
     return out
 
