@@ -219,6 +219,25 @@ __global__ void dump_nchw_kernel(const void* __restrict__ in, int in_pitch, int 
   }
 }
 
+// same, reading the parity planes a stride-2 consumer uses (a producer may store only those)
+__global__ void dump_planes_nchw_kernel(const void* __restrict__ planes, long long plane_rows, int pitch, int C, int batch,
+                                        int H, int W, int is_fp16, float* __restrict__ out) {
+  const long long total = (long long)batch * C * H * W;
+  const int Hq = H / 2 + 2, Wq = W / 2 + 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W);
+    long long r = i / W;
+    const int y = (int)(r % H);
+    r /= H;
+    const int c = (int)(r % C);
+    const int n = (int)(r / C);
+    const int yp = y + 1, xp = x + 1;
+    const size_t row = (size_t)((yp & 1) * 2 + (xp & 1)) * plane_rows + ((size_t)n * Hq + (yp >> 1) + 1) * Wq + (xp >> 1) + 1;
+    out[i] = ld16(planes, row * pitch + c, is_fp16);
+  }
+}
+
 // ---------------------------------------------------------------- reference conv (CUDA cores)
 __global__ void ref_conv_kernel(RefConvParams p) {
   const int Hq = p.Ho + 2, Wq = p.Wo + 2, Hp = p.H + 2, Wp = p.W + 2;
@@ -347,6 +366,14 @@ int launch_copy_channels(const void* in, int in_pitch, int Cp, long long rows, v
 int launch_dump_nchw(const void* in, int in_pitch, int C, int batch, int H, int W, int is_fp16, float* out,
                      cudaStream_t s) {
   dump_nchw_kernel<<<grid_for((long long)batch * C * H * W), 256, 0, s>>>(in, in_pitch, C, batch, H, W, is_fp16, out);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_dump_planes_nchw(const void* planes, long long plane_rows, int pitch, int C, int batch, int H, int W,
+                            int is_fp16, float* out, cudaStream_t s) {
+  dump_planes_nchw_kernel<<<grid_for((long long)batch * C * H * W), 256, 0, s>>>(planes, plane_rows, pitch, C, batch, H, W,
+                                                                               is_fp16, out);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

@@ -60,6 +60,12 @@ struct ConvGemmParams {
   int has_res;           // residual tile added after the activation (shortcut fused)
   int leaky;
   int dbg;               // ablation bits (AY_DBG): 1 no MMA, 2 no operand TMA, 4 no output store, 8 no residual
+  // parity-plane output for a stride-2 consumer (see s2_gather_kernel for the layout):
+  // 0 = rows only, 1 = rows and planes, 2 = planes only
+  int plane_mode;
+  void* planes;
+  long long plane_rows;
+  int plane_pitch;
   // fused YOLO decode (head convolutions)
   int head;
   float* dec_out;        // [B, dec_rows_total, dec_cols]
@@ -95,6 +101,8 @@ int launch_copy_channels(const void* in, int in_pitch, int Cp, long long rows, v
                          cudaStream_t s);
 int launch_dump_nchw(const void* in, int in_pitch, int C, int batch, int H, int W, int is_fp16,
                      float* out, cudaStream_t s);
+int launch_dump_planes_nchw(const void* planes, long long plane_rows, int pitch, int C, int batch, int H, int W,
+                            int is_fp16, float* out, cudaStream_t s);
 struct RefConvParams {
   const void* in; int in_pitch; int Cin_p; int Cin_k; int H, W;   // input (unpadded H,W); Cin_k: weight columns per tap
   const void* w; int ktot;                                     // [Cout_p][taps*Cin_k] 16-bit

@@ -367,6 +367,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const bool zero_row = halo | !in_range;
 
       if (!p.head) {
+        uint4* plane_ptr = nullptr;
+        if (p.plane_mode != 0) {
+          // padded output pixel (yy, xx) -> plane (yy&1, xx&1), position (yy/2 + 1, xx/2 + 1) of the half-size padded grid
+          const int Hq2 = (p.Hp - 2) / 2 + 2, Wq2 = (p.Wp - 2) / 2 + 2;
+          const size_t prow = (size_t)((yy & 1) * 2 + (xx & 1)) * (size_t)p.plane_rows +
+                              ((size_t)img * Hq2 + (yy >> 1) + 1) * Wq2 + (xx >> 1) + 1;
+          plane_ptr = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.planes) + prow * p.plane_pitch + n0);
+        }
         if (has_res && half < nchunks && lane == 0) {            // residual of my first chunk, before the MMAs finish
           wait_buffer_free();
           const uint32_t b = cid % nbuf;
@@ -398,7 +406,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           if (has_res) {
             bar_wait(res_bar(ew, b), (cid / nbuf) & 1u, p.err_flag, 5);
-          } else {
+          } else if (p.plane_mode != 2) {
             if (lane == 0) wait_buffer_free();
             __syncwarp();
           }
@@ -422,12 +430,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             o.z = pack_pair<FP16>(f[8 * q + 4], f[8 * q + 5]);
             o.w = pack_pair<FP16>(f[8 * q + 6], f[8 * q + 7]);
             if (zero_row) o = make_uint4(0u, 0u, 0u, 0u);
-            sts128(addr, o);
+            if (p.plane_mode != 2) sts128(addr, o);
+            if (p.plane_mode != 0 && in_range) plane_ptr[(size_t)c * 4 + q] = o;   // 64 B per row and chunk, straight to HBM
           }
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          __syncwarp();
+          if (p.plane_mode != 2) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();                                          // every lane is done with `buf` (reads and writes)
           if (lane == 0) {
-            if (!(p.dbg & 4)) tma_store_2d(&tmOut, buf, n0 + c * 32, row0);
+            if (!(p.dbg & 4) && p.plane_mode != 2) tma_store_2d(&tmOut, buf, n0 + c * 32, row0);
             if (has_res && c + 2 < nchunks) {                    // residual of my next chunk
               wait_buffer_free();
               const uint32_t b1 = (cid + 1) % nbuf;

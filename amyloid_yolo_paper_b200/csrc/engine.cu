@@ -106,6 +106,9 @@ struct Layer {
   int yolo_layer = -1;
   void* planes = nullptr;           // stride-2: parity planes [4][plane_rows][cin_p]
   long long plane_rows = 0;
+  bool gather_fused = false;        // stride-2: the producer of the input writes the planes itself
+  int plane_consumer = -1;          // conv: index of the stride-2 conv whose planes this conv's epilogue fills
+  int plane_mode = 0;               // conv: 1 = rows and planes, 2 = planes only (nothing else reads the rows)
   float* raw_f32 = nullptr;         // reference path scratch for heads
   // tmA: a_rows x 64-channel box of the input (or parity planes); tmB: BN/2 x 64 box of the weights;
   // tmOut/tmRes: 32-row x 32-channel boxes of the epilogue's TMA store / residual load; tmResPF: L2 prefetch box
@@ -441,6 +444,24 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     }
   }
 
+  // ---- pass 3c: parity planes of stride-2 convolutions; the GEMM that produces their input fills them directly
+  for (int i = 1; i < n_layers; ++i) {
+    Layer& L = Ls[i];
+    if (L.d.type != AY_CONV || L.impl != 1 || L.d.stride != 2) continue;
+    const ActView& in = Ls[i - 1].out;
+    if (!in.ptr) { set_error("layer %d: input of the convolution is not materialised", i); return AY_EINVAL; }
+    L.plane_rows = ay::padded_rows(max_batch, L.H, L.W);
+    AY_TRY(ay::dev_alloc(ctx, &L.planes, (size_t)4 * L.plane_rows * in.Cp * 2, true));
+    int pc = -1;
+    if (Ls[i - 1].d.type == AY_CONV && Ls[i - 1].impl == 1 && !Ls[i - 1].is_head) pc = i - 1;
+    else if (Ls[i - 1].d.type == AY_SHORTCUT && Ls[i - 1].fused_into_prev) pc = i - 2;
+    if (pc >= 0 && Ls[pc].plane_consumer < 0 && in.pitch == in.Cp) {
+      Ls[pc].plane_consumer = i;
+      Ls[pc].plane_mode = explicit_refs[i - 1].empty() ? 2 : 1;
+      L.gather_fused = true;
+    }
+  }
+
   // ---- pass 4: convolution resources
   for (int i = 0; i < n_layers; ++i) {
     Layer& L = Ls[i];
@@ -470,8 +491,6 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     // A boxes are always 64 channels wide; when the tensor stores only 32 (cin_p = 32) the upper half of the
     // box lies outside the tensor and the TMA zero-fills it (the matching weight columns are zero as well)
     if (L.d.stride == 2) {
-      L.plane_rows = ay::padded_rows(max_batch, L.H, L.W);
-      AY_TRY(ay::dev_alloc(ctx, &L.planes, (size_t)4 * L.plane_rows * L.cin_p * 2, true));
       AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, 64, L.a_rows, ctx->is_fp16));
     } else {
       AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, 64, L.a_rows, ctx->is_fp16));
@@ -639,8 +658,10 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
       q.b_tap0[kh] = kh * 3;
     }
   } else {
-    AY_TRY(ay::launch_s2_gather(in.ptr, in.pitch, L.cin_p / 8, batch, in.H, in.W, L.planes, L.plane_rows, st));
-    ++ctx->launches;
+    if (!L.gather_fused) {
+      AY_TRY(ay::launch_s2_gather(in.ptr, in.pitch, L.cin_p / 8, batch, in.H, in.W, L.planes, L.plane_rows, st));
+      ++ctx->launches;
+    }
     q.n_groups = 9;
     for (int kh = 0; kh < 3; ++kh)
       for (int kw = 0; kw < 3; ++kw) {
@@ -668,6 +689,13 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   } else {
     q.has_res = res ? 1 : 0;
     q.cout = L.C;
+    if (L.plane_consumer >= 0) {
+      const Layer& Cn = Ls[L.plane_consumer];
+      q.plane_mode = L.plane_mode;
+      q.planes = Cn.planes;
+      q.plane_rows = Cn.plane_rows;
+      q.plane_pitch = target->Cp;
+    }
   }
   ++ctx->launches;
   return ay::launch_conv_gemm(L.tmA, L.tmB, L.tmOut, L.tmRes, L.tmResPF, q, L.G, ctx->is_fp16, ctx->num_sms, st);
@@ -758,6 +786,15 @@ extern "C" int ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out
   }
   const Layer& L = ctx->layers[layer];
   if (!L.out.ptr) { set_error("layer %d is fused into its consumer and has no stored output", layer); return AY_EINVAL; }
+  // a tensor read only by a stride-2 convolution is stored as that convolution's parity planes
+  int producer = -1;
+  if (L.d.type == AY_CONV && L.fused_shortcut < 0) producer = layer;
+  else if (L.d.type == AY_SHORTCUT && L.fused_into_prev) producer = layer - 1;
+  if (!ctx->use_ref && producer >= 0 && ctx->layers[producer].plane_mode == 2) {
+    const Layer& Cn = ctx->layers[ctx->layers[producer].plane_consumer];
+    return ay::launch_dump_planes_nchw(Cn.planes, Cn.plane_rows, L.out.Cp, L.C, batch, L.H, L.W, ctx->is_fp16, out_nchw,
+                                       static_cast<cudaStream_t>(stream));
+  }
   return ay::launch_dump_nchw(L.out.ptr, L.out.pitch, L.C, batch, L.H, L.W, ctx->is_fp16, out_nchw,
                               static_cast<cudaStream_t>(stream));
 }
