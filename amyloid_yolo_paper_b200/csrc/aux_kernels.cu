@@ -100,6 +100,33 @@ __global__ void first_conv_kernel(FirstConvParams p) {
   }
 }
 
+// ---------------------------------------------------------------- input staging for the first convolution
+// ToTensor (/255) + nearest Resize (utils/transforms.py:89-111) into a zero-haloed NHWC tensor with 8 channels
+// (3 used) per pixel: 16 bytes per pixel, so that three horizontally adjacent pixels are 24 contiguous
+// elements and one TMA row of the first layer's A operand (see engine.cu, first layer).
+__global__ void prep_input_kernel(FirstConvParams p) {
+  const int Sp = p.S + 2;
+  const long long total = (long long)p.batch * Sp * Sp;
+  const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= total) return;
+  const int n = (int)(m / ((long long)Sp * Sp));
+  const int pix = (int)(m - (long long)n * Sp * Sp);
+  const int y = pix / Sp - 1, x = pix - (pix / Sp) * Sp - 1;
+  float v[3] = {0.f, 0.f, 0.f};
+  if (y >= 0 && y < p.S && x >= 0 && x < p.S) {
+    if (p.in_kind == AY_IN_F32_NCHW) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = __ldg(static_cast<const float*>(p.in) + (((size_t)n * 3 + c) * p.S + y) * p.S + x);
+    } else {
+      const int sy = __ldg(p.idx_y + y), sx = __ldg(p.idx_x + x);
+      const uint8_t* src = static_cast<const uint8_t*>(p.in) + (((size_t)n * p.src_h + sy) * p.src_w + sx) * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = __fdiv_rn((float)__ldg(src + c), 255.0f);
+    }
+  }
+  reinterpret_cast<uint4*>(p.out)[m] = make_uint4(pack16(v[0], v[1], p.is_fp16), pack16(v[2], 0.f, p.is_fp16), 0u, 0u);
+}
+
 // ---------------------------------------------------------------- stride-2 gather
 // planes[pl][n][a][b][:] = in[n][2(a-1)+ph][2(b-1)+pw][:]  (padded input coords; zero when
 // out of range), a in [0,Ho+2), b in [0,Wo+2), pl = ph*2+pw.  Output tap (kh,kw) of padded
@@ -313,6 +340,13 @@ int launch_first_conv(const FirstConvParams& p, cudaStream_t s) {
   const long long grid = (total + block - 1) / block;
   const size_t smem = (size_t)(p.cout * 28) * sizeof(float);
   first_conv_kernel<<<(unsigned)grid, block, smem, s>>>(p);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_prep_input(const FirstConvParams& p, cudaStream_t s) {
+  const long long total = (long long)p.batch * (p.S + 2) * (p.S + 2);
+  prep_input_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(p);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

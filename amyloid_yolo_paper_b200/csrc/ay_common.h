@@ -89,6 +89,7 @@ struct FirstConvParams {
   void* out; int out_pitch; int Cp; int is_fp16;
 };
 int launch_first_conv(const FirstConvParams& p, cudaStream_t s);
+int launch_prep_input(const FirstConvParams& p, cudaStream_t s);   // p.out = [B,S+2,S+2,8] 16-bit
 int launch_s2_gather(const void* in, int in_pitch, int C8, int batch, int H, int W,
                      void* planes, long long plane_rows, cudaStream_t s);
 int launch_upsample2(const void* in, int in_pitch, int Cp, int batch, int H, int W,

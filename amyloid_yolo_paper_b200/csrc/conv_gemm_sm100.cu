@@ -234,7 +234,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       bar_init(tfull_bar(a), 1);                // tcgen05.commit multicast
-      bar_init(tempty_bar(a), 2 * kEpiWarps);   // leader's copy: 8 epilogue warps x 2 CTAs
+      // leader's copy: the epilogue warps of both CTAs that work on a tile (all 8, or 4 when BN = 32: see `split`)
+      bar_init(tempty_bar(a), p.BN == 32 ? kEpiWarps : 2 * kEpiWarps);
     }
     for (int w = 0; w < kEpiWarps; ++w)
       for (int b = 0; b < kMaxStageBufs; ++b) bar_init(res_bar(w, b), 1);   // residual TMA loads, per epilogue warp
@@ -348,12 +349,19 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int hw = p.Hp * p.Wp;
     const int nchunks = p.BN >> 5;
     uint32_t cid = 0;                                            // chunks processed by this warp -> buffer and barrier phase
-    int acc = 0;
-    uint32_t acc_phase = 0;
+    // A tile with a single 32-column chunk would leave half of the epilogue warps idle and make the per-tile
+    // latency chain (wait, tcgen05.ld, math, store, arrive) the bound; there the two warps of a quarter take
+    // alternate TILES instead of alternate chunks (tile parity = accumulator buffer = `half`).
+    const bool split = nchunks == 1;
+    const int c_first = split ? 0 : half;
     auto wait_buffer_free = [&]() {      // all but the newest (nbuf-1) bulk stores of this thread have read their buffer
       if (nbuf == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
     };
-    for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+    int it = 0;
+    for (int tile = first_tile; tile < total_tiles; tile += n_clusters, ++it) {
+      if (split && (it & 1) != half) continue;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
       const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
       const int n0 = (tile % p.num_n_tiles) * p.BN;
       const int row0 = m0 + quarter * 32;                        // first of this warp's 32 rows
@@ -375,16 +383,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                               ((size_t)img * Hq2 + (yy >> 1) + 1) * Wq2 + (xx >> 1) + 1;
           plane_ptr = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.planes) + prow * p.plane_pitch + n0);
         }
-        if (has_res && half < nchunks && lane == 0) {            // residual of my first chunk, before the MMAs finish
+        if (has_res && c_first < nchunks && lane == 0) {         // residual of my first chunk, before the MMAs finish
           wait_buffer_free();
           const uint32_t b = cid % nbuf;
           bar_expect_tx(res_bar(ew, b), kStageBufBytes);
-          tma_load_local(&tmRes, res_bar(ew, b), stg + b * kStageBufBytes, n0 + half * 32, row0);
+          tma_load_local(&tmRes, res_bar(ew, b), stg + b * kStageBufBytes, n0 + c_first * 32, row0);
         }
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
         fence_after();
         const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
-        for (int c = half; c < nchunks; c += 2, ++cid) {
+        for (int c = c_first; c < nchunks; c += 2, ++cid) {
           const uint32_t b = cid % nbuf;
           const uint32_t buf = stg + b * kStageBufBytes;
           uint32_t v[32];
@@ -455,7 +463,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols +
                        ((size_t)gy * Gd + gx) * p.dec_cols;
         const size_t a_step = (size_t)Gd * Gd * p.dec_cols;
-        for (int c = half; c < nchunks; c += 2) {
+        for (int c = c_first; c < nchunks; c += 2) {
           uint32_t v[32];
           tmem_load32(t_acc + (uint32_t)(c * 32), v);
           const int ch0 = n0 + c * 32;
@@ -481,7 +489,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       fence_before();
       __syncwarp();
       if (lane == 0) bar_arrive_remote(map_to_cta(tempty_bar(acc), 0));
-      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores have left shared memory and landed
   }

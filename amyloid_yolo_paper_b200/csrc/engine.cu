@@ -95,7 +95,9 @@ struct Layer {
   // convolution
   int cin = 0, cin_p = 0, cin_k = 0, cout_rows = 0, ktot = 0;   // cin_p: channels stored (x32); cin_k: K per tap (x64)
   int BN = 0, G = 1, a_rows = 128, stages = 0, nbuf = 1;
-  int impl = 0;                     // 0 none, 1 tcgen05 gemm, 2 first-layer direct
+  int impl = 0;                     // 0 none, 1 tcgen05 gemm
+  bool first = false;               // 3-channel first layer: GEMM over the staged 8-channel input x8
+  void* x8 = nullptr;               // [B, S+2, S+2, 8] 16-bit (first layer only)
   void* w16 = nullptr;              // [cout_rows][ktot] 16-bit (gemm)
   float* w32 = nullptr;             // [cout][27] fp32 (first layer)
   float* bias = nullptr;            // [cout_rows]
@@ -380,7 +382,8 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
         if (L.d.size != 3 || L.d.stride != 1 || in_channels != 3) {
           set_error("first convolution must be 3x3 stride 1 over 3 channels"); return AY_EINVAL;
         }
-        L.impl = 2;
+        L.impl = 1;
+        L.first = true;
       } else {
         L.impl = 1;
         if (L.d.stride == 2 && (L.d.size != 3 || (Ls[i - 1].H & 1) || (Ls[i - 1].W & 1))) {
@@ -462,26 +465,37 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     }
   }
 
+  const int ph0 = img_size, pw0 = img_size;
   // ---- pass 4: convolution resources
   for (int i = 0; i < n_layers; ++i) {
     Layer& L = Ls[i];
     if (L.d.type != AY_CONV) continue;
-    if (L.impl == 2) {
-      AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.w32), sizeof(float) * L.C * 27, true));
-      AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.C, true));
-      continue;
+    if (L.first) {
+      // First layer as a GEMM with K = 3 (kh) x 64: the A row of output pixel (y, x) and tap row kh is the 24
+      // contiguous elements of the three 8-channel pixels (y+kh-1, x-1..x+1) of x8.  The tensor map declares 24
+      // inner elements and a row stride of ONE pixel (16 B), i.e. overlapping rows; elements 24..63 of the 64-wide
+      // box are out of bounds and zero-filled.  Weight column kh*64 + kw*8 + c.
+      AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.w32), sizeof(float) * L.C * 27, true));   // reference path
+      const long long rows8 = ay::padded_rows(max_batch, ph0, pw0);
+      AY_TRY(ay::dev_alloc(ctx, &L.x8, (size_t)rows8 * 8 * 2, true));
+      L.cin_p = 8;
+      L.cin_k = 64;
+      L.ktot = 3 * 64;
     }
-    const ActView& in = Ls[i - 1].out;
-    if (!in.ptr) { set_error("layer %d: input of the convolution is not materialised", i); return AY_EINVAL; }
+    static const ActView no_view;
+    const ActView& in = L.first ? no_view : Ls[i - 1].out;
+    if (!L.first && !in.ptr) { set_error("layer %d: input of the convolution is not materialised", i); return AY_EINVAL; }
     const int taps = L.d.size * L.d.size;
-    L.cin_p = in.Cp;
-    L.cin_k = ay::round_up(L.cin_p, 64);
-    L.ktot = taps * L.cin_k;
+    if (!L.first) {
+      L.cin_p = in.Cp;
+      L.cin_k = ay::round_up(L.cin_p, 64);
+      L.ktot = taps * L.cin_k;
+    }
     const int cout_p = ay::round_up(L.C, 32);
     if (L.is_head) L.BN = cout_p <= 256 ? cout_p : 256;
     else L.BN = (cout_p % 256 == 0) ? 256 : (cout_p % 128 == 0) ? 128 : (cout_p % 64 == 0) ? 64 : 32;
     L.cout_rows = ay::round_up(cout_p, L.BN);
-    L.G = (L.d.size == 3 && L.d.stride == 1) ? 3 : 1;
+    L.G = (L.d.size == 3 && L.d.stride == 1 && !L.first) ? 3 : 1;
     L.a_rows = L.G == 3 ? 130 : 128;
     ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, &L.stages, &L.nbuf);
     if (L.stages < 2) { set_error("layer %d: tile does not fit in shared memory", i); return AY_EINVAL; }
@@ -490,7 +504,9 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     AY_TRY(ay::make_map_2d(&L.tmB, L.w16, L.ktot, L.cout_rows, L.ktot, 64, L.BN / 2, ctx->is_fp16));
     // A boxes are always 64 channels wide; when the tensor stores only 32 (cin_p = 32) the upper half of the
     // box lies outside the tensor and the TMA zero-fills it (the matching weight columns are zero as well)
-    if (L.d.stride == 2) {
+    if (L.first) {
+      AY_TRY(ay::make_map_2d(&L.tmA, L.x8, 24, ay::padded_rows(max_batch, ph0, pw0), 8, 64, L.a_rows, ctx->is_fp16));
+    } else if (L.d.stride == 2) {
       AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, 64, L.a_rows, ctx->is_fp16));
     } else {
       AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, 64, L.a_rows, ctx->is_fp16));
@@ -525,13 +541,20 @@ extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const flo
   }
   Layer& L = ctx->layers[layer];
   const int k = L.d.size, taps = k * k, cout = L.C, cin = L.cin;
-  if (L.impl == 2) {
+  if (L.first) {
     std::vector<float> r((size_t)cout * 27);
+    std::vector<uint16_t> r16((size_t)L.cout_rows * L.ktot, 0);
     for (int o = 0; o < cout; ++o)
       for (int c = 0; c < 3; ++c)
-        for (int t = 0; t < 9; ++t) r[(size_t)o * 27 + t * 3 + c] = w[((size_t)o * 3 + c) * 9 + t];
+        for (int t = 0; t < 9; ++t) {
+          r[(size_t)o * 27 + t * 3 + c] = w[((size_t)o * 3 + c) * 9 + t];
+          r16[(size_t)o * L.ktot + (t / 3) * 64 + (t % 3) * 8 + c] = ay::to16(w[((size_t)o * 3 + c) * 9 + t], ctx->is_fp16);
+        }
+    std::vector<float> b(L.cout_rows, 0.f);
+    memcpy(b.data(), bias, sizeof(float) * cout);
     AY_CUDA(cudaMemcpy(L.w32, r.data(), r.size() * sizeof(float), cudaMemcpyHostToDevice));
-    AY_CUDA(cudaMemcpy(L.bias, bias, sizeof(float) * cout, cudaMemcpyHostToDevice));
+    AY_CUDA(cudaMemcpy(L.w16, r16.data(), r16.size() * 2, cudaMemcpyHostToDevice));
+    AY_CUDA(cudaMemcpy(L.bias, b.data(), sizeof(float) * L.cout_rows, cudaMemcpyHostToDevice));
   } else {
     std::vector<uint16_t> r((size_t)L.cout_rows * L.ktot, 0);
     for (int o = 0; o < cout; ++o)
@@ -602,15 +625,18 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   std::vector<Layer>& Ls = ctx->layers;
   Layer& L = Ls[i];
   const ActView* target = L.fused_shortcut >= 0 ? &Ls[L.fused_shortcut].out : &L.out;
-  if (L.impl == 2) {
+  if (L.first) {
     ay::FirstConvParams p{};
     p.in = input; p.in_kind = in_kind; p.batch = batch; p.S = ctx->img_size; p.src_h = src_h; p.src_w = src_w;
     p.idx_y = ctx->idx_y; p.idx_x = ctx->idx_x; p.w = L.w32; p.bias = L.bias; p.cout = L.C; p.leaky = L.d.leaky;
     p.out = target->ptr; p.out_pitch = target->pitch; p.Cp = target->Cp; p.is_fp16 = ctx->is_fp16;
     ++ctx->launches;
-    return ay::launch_first_conv(p, st);
+    if (ctx->use_ref) return ay::launch_first_conv(p, st);   // fp32 CUDA-core reference of this layer
+    p.out = L.x8;
+    AY_TRY(ay::launch_prep_input(p, st));
   }
-  const ActView& in = Ls[i - 1].out;
+  static const ActView no_view;
+  const ActView& in = L.first ? no_view : Ls[i - 1].out;
   const int Hq = L.H + 2, Wq = L.W + 2;
   const ActView* res = L.residual_src >= 0 ? &Ls[L.residual_src].out : nullptr;
   const Layer* Y = L.is_head ? &Ls[L.yolo_layer] : nullptr;
@@ -647,7 +673,14 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   q.num_n_tiles = L.cout_rows / L.BN;
   q.a_rows = L.a_rows;
   q.kb_per_tap = L.cin_k / 64;
-  if (L.d.size == 1) {
+  if (L.first) {
+    q.n_groups = 3;                       // one group per kh; K of a group = the 3 pixels x 8 channels of that row
+    q.kb_per_tap = 1;
+    for (int kh = 0; kh < 3; ++kh) {
+      q.a_row_off[kh] = (kh - 1) * Wq - 1;
+      q.b_tap0[kh] = kh;
+    }
+  } else if (L.d.size == 1) {
     q.n_groups = 1;
     q.a_row_off[0] = 0;
     q.b_tap0[0] = 0;
