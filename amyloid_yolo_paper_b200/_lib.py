@@ -95,6 +95,10 @@ _PROTOTYPES = {
                     ctypes.c_void_p, ctypes.c_void_p],
     "ay_check": [ctypes.c_void_p, ctypes.c_void_p],
     "ay_net_use_reference_conv": [ctypes.c_void_p, ctypes.c_int],
+    "ay_forward_profile": [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                           ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_float), ctypes.c_int],
+    "ay_debug_set": [ctypes.c_void_p, ctypes.c_int],
+    "ay_debug_counters": [ctypes.c_void_p, ctypes.POINTER(ctypes.c_ulonglong), ctypes.c_int],
 }
 
 

@@ -36,7 +36,8 @@ __device__ __forceinline__ uint32_t pack16(float lo, float hi, int is_fp16) {
 
 // ---------------------------------------------------------------- first conv
 // One thread per padded output pixel; all output channels in registers, 32 at a time.
-// Arithmetic in fp32 on fp32 weights (this layer is 0.5 % of the FLOPs and HBM-bound).
+// Test reference of the first layer: fp32 arithmetic on the same 16-bit-rounded operands as the tensor-core path
+// (pixel values 0..255, weights / 255).
 __global__ void first_conv_kernel(FirstConvParams p) {
   extern __shared__ float sw[];  // [cout][27] then bias[cout]
   const int nw = p.cout * 27;
@@ -67,12 +68,14 @@ __global__ void first_conv_kernel(FirstConvParams p) {
         float v = 0.f;
         if (ok) {
           if (p.in_kind == AY_IN_F32_NCHW) {
-            v = __ldg(static_cast<const float*>(p.in) + (((size_t)n * 3 + c) * p.S + iy) * p.S + ix);
+            v = 255.0f * __ldg(static_cast<const float*>(p.in) + (((size_t)n * 3 + c) * p.S + iy) * p.S + ix);
+            const uint16_t r16 = cvt16(v, p.is_fp16);          // same rounding as the staged 16-bit input of the GEMM path
+            v = ld16(&r16, 0, p.is_fp16);
           } else {
             const int sy = __ldg(p.idx_y + iy), sx = __ldg(p.idx_x + ix);
             const uint8_t u = __ldg(static_cast<const uint8_t*>(p.in) +
                                     (((size_t)n * p.src_h + sy) * p.src_w + sx) * 3 + c);
-            v = __fdiv_rn((float)u, 255.0f);
+            v = (float)u;                                      // 1/255 is folded into the weights
           }
         }
         in[(kh * 3 + kw) * 3 + c] = v;
@@ -116,12 +119,12 @@ __global__ void prep_input_kernel(FirstConvParams p) {
   if (y >= 0 && y < p.S && x >= 0 && x < p.S) {
     if (p.in_kind == AY_IN_F32_NCHW) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) v[c] = __ldg(static_cast<const float*>(p.in) + (((size_t)n * 3 + c) * p.S + y) * p.S + x);
+      for (int c = 0; c < 3; ++c) v[c] = 255.0f * __ldg(static_cast<const float*>(p.in) + (((size_t)n * 3 + c) * p.S + y) * p.S + x);
     } else {
       const int sy = __ldg(p.idx_y + y), sx = __ldg(p.idx_x + x);
       const uint8_t* src = static_cast<const uint8_t*>(p.in) + (((size_t)n * p.src_h + sy) * p.src_w + sx) * 3;
 #pragma unroll
-      for (int c = 0; c < 3; ++c) v[c] = __fdiv_rn((float)__ldg(src + c), 255.0f);
+      for (int c = 0; c < 3; ++c) v[c] = (float)__ldg(src + c);   // 0..255 is exact in bf16; the 1/255 of ToTensor is folded into the weights
     }
   }
   reinterpret_cast<uint4*>(p.out)[m] = make_uint4(pack16(v[0], v[1], p.is_fp16), pack16(v[2], 0.f, p.is_fp16), 0u, 0u);

@@ -54,10 +54,17 @@ struct ConvGemmParams {
   int a_rows;            // rows of the A box (128, or 130 with tap reuse)
   int BN;                // N of the pair tile (each CTA loads BN/2 weight rows)
   int num_stages;
+  int units_per_stage;   // (group, k-block) units loaded and consumed per pipeline stage (divides n_groups*kb_per_tap)
+  int num_acc;           // TMEM accumulator buffers (512 / BN, at most 16)
+  int b_resident;        // this CTA's half of ALL weight tiles stays in shared memory for the whole launch
+  int b_res_tiles;       // number of [BN/2 x 64] weight tiles (= K / 64)
+  int a_mode;            // 0: 128B-swizzled [a_rows x 64 ch] boxes; 1: first layer, 8-channel pixels read unswizzled
   int nbuf;              // epilogue staging buffers per warp (1 or 2)
   int Hp, Wp;            // padded output size (halo test)
   const float* bias;     // [num_n_tiles*BN]
   int has_res;           // residual tile added after the activation (shortcut fused)
+  void* out_ptr; int out_pitch;          // output rows (16-bit elements), channel 0 of this layer's slice
+  const void* res_ptr; int res_pitch;    // residual rows
   int leaky;
   int dbg;               // ablation bits (AY_DBG): 1 no MMA, 2 no operand TMA, 4 no output store, 8 no residual
   // parity-plane output for a stride-2 consumer (see s2_gather_kernel for the layout):
@@ -73,12 +80,13 @@ struct ConvGemmParams {
   float stride;
   float anchor_w[8], anchor_h[8];   // already divided by stride (models.py:122)
   unsigned int* err_flag;
+  unsigned long long* prof;   // 16 cycle counters of CTA 0 (profiling runs only), else nullptr
 };
 int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
                      const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
                      cudaStream_t stream);
-int conv_gemm_stage_bytes(int BN, int G, int a_rows);
-void conv_gemm_pick_smem(int BN, int G, int a_rows, int* stages, int* nbuf);
+int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident);
+void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int* stages, int* nbuf);
 
 // aux_kernels.cu ------------------------------------------------------------
 struct FirstConvParams {

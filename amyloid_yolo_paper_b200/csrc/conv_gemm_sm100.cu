@@ -58,6 +58,19 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+// one lane of a converged warp.  The producer and MMA warps run their loops with all 32 lanes and predicate only the
+// TMA / tcgen05 instructions on this: under `if (lane == 0)` every operand counts as divergent and ptxas wraps each
+// UTCHMMA / UTMALDG in a VOTEU-ELECT-R2UR.BROADCAST loop (~115 cycles per MMA, measured), which made the issuing
+// thread the bound of every layer with N < 256.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -155,6 +168,8 @@ __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + ex
 // ---- epilogue staging: 32 rows x 32 channels (64-byte rows, TMA SWIZZLE_64B layout), nbuf (1|2) buffers per warp ----
 constexpr uint32_t kStageBufBytes = 32 * 64;
 constexpr int kMaxStageBufs = 2;
+constexpr int kMaxChunksPerWarp = 4;     // BN <= 256: 8 chunks of 32 columns, two warps per TMEM lane quarter
+constexpr int kMaxAcc = 16;             // TMEM accumulators: 512 columns / BN
 constexpr int kBiasFloats = 1024;
 constexpr int kBK = 64;                 // channels per k-block: one 128-byte swizzle row
 constexpr uint32_t kRowBytes = 128;
@@ -180,6 +195,17 @@ template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
+// 256-bit global accesses (sm_100): a thread moves one whole 32-byte sector per instruction
+__device__ __forceinline__ void ldg256(const void* ptr, uint32_t* v) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "l"(ptr));
+}
+__device__ __forceinline__ void stg256(void* ptr, const uint32_t* v) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+               ::"l"(ptr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
 __device__ __forceinline__ void lds128(uint32_t addr, uint4& v) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
 }
@@ -198,27 +224,37 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t smem_base = (smem_addr(smem_raw) + 1023u) & ~1023u;
   const uint32_t a_region = (uint32_t)((p.a_rows + 7) & ~7) * kRowBytes;    // multiple of 1024
   const uint32_t b_tile = (uint32_t)(p.BN / 2) * kRowBytes;
-  const uint32_t stage_bytes = a_region + G * b_tile;
-  const uint32_t tx_bytes = (uint32_t)p.a_rows * kRowBytes + G * b_tile;    // what one CTA's TMA loads deliver
+  // resident weights: when this CTA's half of the whole weight matrix fits beside the A ring it is loaded once per
+  // launch and the ring holds A boxes only (early layers: hundreds of tiles per CTA re-reading the same few KB)
+  const uint32_t res_bytes = p.b_resident ? (uint32_t)p.b_res_tiles * b_tile : 0u;
+  const uint32_t ring_base = smem_base + res_bytes;
+  const int U = p.units_per_stage;                    // (group, k-block) units per pipeline stage
+  const uint32_t unit_bytes = a_region + (p.b_resident ? 0u : G * b_tile);
+  const uint32_t stage_bytes = (uint32_t)U * unit_bytes;
+  const uint32_t tx_bytes = (uint32_t)U * ((uint32_t)p.a_rows * kRowBytes + (p.b_resident ? 0u : G * b_tile));   // one CTA's loads per stage
   const int S = p.num_stages;
-  const int nbuf = p.nbuf;
-  const uint32_t staging_base = smem_base + S * stage_bytes;
-  const uint32_t bar_base = staging_base + (uint32_t)(kEpiWarps * nbuf) * kStageBufBytes;
+  const uint32_t staging_base = ring_base + S * stage_bytes;
+  const uint32_t bar_base = staging_base;           // (the epilogue stages nothing in shared memory any more)
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * S + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + 2 + a); };
-  auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * S + 4 + w * kMaxStageBufs + b); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * S + 4 + kEpiWarps * kMaxStageBufs);
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + kMaxAcc + a); };
+  auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * S + 2 * kMaxAcc + w * kMaxStageBufs + b); };
+  const uint32_t dummy_bar = bar_base + 8u * (2 * S + 2 * kMaxAcc + kEpiWarps * kMaxStageBufs);
+  const uint32_t bres_bar = dummy_bar + 8u;
+  const uint32_t tmem_slot = bres_bar + 8u;
   // whole-layer bias staged once: with this much shared memory the L1 is ~1 KB, so a global bias load
   // would be an L2 round trip in the middle of the epilogue's dependency chain
-  float* s_bias = reinterpret_cast<float*>(smem_raw + (tmem_slot - smem_addr(smem_raw)) + 16u);
+  float* s_bias = reinterpret_cast<float*>(smem_raw + (((tmem_slot + 4u + 15u) & ~15u) - smem_addr(smem_raw)));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_rank();
+  const uint32_t rank = blockIdx.x & 1u;            // == %cluster_ctarank for __cluster_dims__(2,1,1); warp-uniform
   const bool leader = rank == 0;
-  const uint32_t tmem_cols = (p.BN <= 16) ? 32u : (p.BN <= 32) ? 64u : (p.BN <= 64) ? 128u : (p.BN <= 128) ? 256u : 512u;
+  // all 512 TMEM columns (one CTA per SM): 512/BN accumulators, so that the MMA issuer runs that many tiles ahead
+  // of the epilogue and the commit -> epilogue -> arrive round trip is off the critical path of small tiles
+  const uint32_t tmem_cols = 512u;
+  const int num_acc = (p.dbg & 32) ? 2 : p.num_acc;
   const bool has_res = p.has_res && !(p.dbg & 8);
 
   if (warp == 0 && lane == 0) {
@@ -229,10 +265,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < S; ++s) {
-      bar_init(full_bar(s), 1);     // leader's copy is the one in use: 1 arrive.expect_tx + bytes of both CTAs
+      // leader's copy is the one in use: 1 arrive.expect_tx + bytes of both CTAs (ablation without loads: an
+      // arrive of each CTA's producer, so that the pair stays in step)
+      bar_init(full_bar(s), (p.dbg & 2) ? 2 : 1);
       bar_init(empty_bar(s), 1);    // tcgen05.commit multicast
     }
-    for (int a = 0; a < 2; ++a) {
+    bar_init(dummy_bar, 1);
+    bar_init(bres_bar, 1);
+    for (int a = 0; a < kMaxAcc; ++a) {
       bar_init(tfull_bar(a), 1);                // tcgen05.commit multicast
       // leader's copy: the epilogue warps of both CTAs that work on a tile (all 8, or 4 when BN = 32: see `split`)
       bar_init(tempty_bar(a), p.BN == 32 ? kEpiWarps : 2 * kEpiWarps);
@@ -253,51 +293,74 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+  if (tmem_base != 0u) {       // all 512 columns of an otherwise idle SM: the MMA warp relies on base 0 (uniform operand)
+    if (p.err_flag) atomicExch(p.err_flag, 0xDEAD0200u);
+    __trap();
+  }
 
+  // cycle counters of one representative CTA (tools/layer_times.py --counters): [0] producer waiting for a free
+  // stage, [1] producer issuing loads, [2] MMA thread waiting for a free accumulator, [3] waiting for operands,
+  // [4] issuing MMAs + commit, [5] MMA thread total, [6] tiles, [7] stages, [8] epilogue warp 0 busy+waiting, [9] its tiles
+  const bool prof = p.prof != nullptr && blockIdx.x == 0;
+  long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const long long t_start = prof ? clock64() : 0;
   const int total_tiles = p.num_m_tiles * p.num_n_tiles;
   const int n_clusters = gridDim.x >> 1;
   const int first_tile = blockIdx.x >> 1;
-  const int units = p.n_groups * p.kb_per_tap;      // pipeline stages consumed per tile
+  const int stages_per_tile = p.n_groups * p.kb_per_tap / U;
 
+  // shared::cluster address of the LEADER's copy of a barrier: the CTA rank sits in bit 24 of the window address
+  constexpr uint32_t kLeaderMask = 0xFEFFFFFFu;
   if (warp == 0) {
-    if (lane == 0) {
+    {
       int stage = 0;
       uint32_t phase = 0;
-      // The residual tile (128 rows x BN channels of this CTA) is pulled into L2 one tile ahead: the epilogue's
-      // small TMA loads then see L2 latency instead of HBM latency, with no shared-memory cost for the bytes in flight.
-      if (has_res && first_tile < total_tiles)
-        tma_prefetch_l2(&tmResPF, (first_tile % p.num_n_tiles) * p.BN,
-                        (first_tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta);
+      if (p.b_resident && elect_one()) {
+        const uint32_t lead_bres = bres_bar & kLeaderMask;
+        if (leader) bar_expect_tx(bres_bar, 2u * res_bytes);
+        for (int t = 0; t < p.b_res_tiles; ++t)
+          tma_load_pair(&tmB, lead_bres, smem_base + (uint32_t)t * b_tile, t * kBK, (int)rank * (p.BN / 2));
+      }
+      __syncwarp();
       for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
         const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
         const int n0 = (tile % p.num_n_tiles) * p.BN + (int)rank * (p.BN / 2);
-        if (has_res && tile + n_clusters < total_tiles) {
-          const int nt = tile + n_clusters;
-          tma_prefetch_l2(&tmResPF, (nt % p.num_n_tiles) * p.BN, (nt / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta);
-        }
-        for (int g = 0; g < p.n_groups; ++g) {
-          const int arow = m0 + p.a_row_off[g];
-          const int bcol0 = p.b_tap0[g] * p.kb_per_tap * kBK;
-          for (int kb = 0; kb < p.kb_per_tap; ++kb) {
-            bar_wait(empty_bar(stage), phase ^ 1u, p.err_flag, 1);
-            const uint32_t lead_full = map_to_cta(full_bar(stage), 0);
-            if (p.dbg & 2) {                                   // ablation: no operand loads
-              if (leader) bar_expect_tx(full_bar(stage), 0u);
-            } else {
-              if (leader) bar_expect_tx(full_bar(stage), 2u * tx_bytes);
-              const uint32_t sa = smem_base + stage * stage_bytes;
-              tma_load_pair(&tmA, lead_full, sa, kb * kBK, arow);
+        // a pipeline stage holds U consecutive (group, k-block) units: one barrier round trip per stage
+        int g = 0, kb = 0;
+        for (int st = 0; st < stages_per_tile; ++st) {
+          const long long c0 = prof ? clock64() : 0;
+          bar_wait(empty_bar(stage), phase ^ 1u, p.err_flag, 1);
+          __syncwarp();
+          const long long c1 = prof ? clock64() : 0;
+          const uint32_t lead_full = full_bar(stage) & kLeaderMask;
+          const bool el = elect_one();
+          const bool load = el && !(p.dbg & 2);
+          if (el && (p.dbg & 2)) bar_arrive_remote(lead_full);          // ablation: no operand loads
+          if (load && leader) bar_expect_tx(full_bar(stage), 2u * tx_bytes);
+          uint32_t sa = ring_base + stage * stage_bytes;
+          for (int u = 0; u < U; ++u, sa += unit_bytes) {
+            if (load) {
+              const int arow = m0 + p.a_row_off[g];
+              if (p.a_mode == 1) tma_load_pair(&tmA, lead_full, sa, 0, arow >> 3);   // 8 pixels per 128-byte row
+              else tma_load_pair(&tmA, lead_full, sa, kb * kBK, arow);
+              if (!p.b_resident) {
+                const int bcol0 = g * G * p.kb_per_tap * kBK;       // weight taps of group g are g*G .. g*G+G-1
 #pragma unroll
-              for (int j = 0; j < G; ++j)
-                tma_load_pair(&tmB, lead_full, sa + a_region + j * b_tile, bcol0 + (j * p.kb_per_tap + kb) * kBK, n0);
+                for (int j = 0; j < G; ++j)
+                  tma_load_pair(&tmB, lead_full, sa + a_region + j * b_tile, bcol0 + (j * p.kb_per_tap + kb) * kBK, n0);
+              }
             }
-            if (++stage == S) { stage = 0; phase ^= 1u; }
+            if (++kb == p.kb_per_tap) { kb = 0; ++g; }
           }
+          __syncwarp();
+          if (prof) { pc[0] += c1 - c0; pc[1] += clock64() - c1; }
+          if (++stage == S) { stage = 0; phase ^= 1u; }
         }
       }
+      if (prof && lane == 0) { atomicAdd(p.prof + 0, (unsigned long long)pc[0]); atomicAdd(p.prof + 1, (unsigned long long)pc[1]); }
     }
   } else if (warp == 1) {
-    if (leader && lane == 0) {
+    if (leader) {
       // instruction descriptor: D=f32, A/B = bf16|f16, both K-major, N = BN, M = 256 (pair)
       constexpr uint32_t fmt = FP16 ? 0u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(p.BN >> 3) << 17) |
@@ -306,34 +369,79 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // starts j rows (j*128 B) into the A box: the swizzle is a function of the absolute shared-memory address, so
       // the base-offset field stays 0 (measured on B200: setting it to j gives wrong results).
       constexpr uint64_t desc_hi = (2ull << 61) | (1ull << 46) | (64ull << 32);
+      // first layer (a_mode 1): the A box is 18 rows of 8 pixels x 8 channels, i.e. 144 consecutive pixels of 16 bytes,
+      // read WITHOUT swizzle as overlapping core matrices: 8 consecutive pixels are one 8-row x 16-byte core matrix,
+      // the next 8 rows are 128 B further (SBO) and the next 8-element K chunk is the NEXT pixel, 16 B further (LBO).
+      // One K=16 MMA therefore contracts taps (kw0,kw1) of a filter row, a second one (kw2, +1 pixel x zero weights).
+      constexpr uint64_t desc_a1 = (0ull << 61) | (1ull << 46) | (8ull << 32) | (1ull << 16);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
-        bar_wait(tempty_bar(acc), acc_phase ^ 1u, p.err_flag, 2);
+      const uint32_t b_step = p.b_resident ? (uint32_t)p.kb_per_tap * (b_tile >> 4) : (b_tile >> 4);   // tap j+1 of a group
+      if (p.b_resident) {
+        bar_wait(bres_bar, 0u, p.err_flag, 6);
+        __syncwarp();
         fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.BN);
-        for (int it = 0; it < units; ++it) {
+      }
+      for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
+        const long long c0 = prof ? clock64() : 0;
+        bar_wait(tempty_bar(acc), acc_phase ^ 1u, p.err_flag, 2);
+        __syncwarp();
+        fence_after();
+        if (prof) { pc[2] += clock64() - c0; pc[6] += 1; }
+        const uint32_t d_tmem = (uint32_t)(acc * p.BN);    // tmem_base == 0 (checked after the allocation)
+        const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta);
+        // groups and k-blocks as nested loops with running addresses: the issuing warp has nothing to hide latency
+        // with, so every dependent scalar instruction between two barriers (a division, an indexed constant load)
+        // shows up in the layer time
+        uint32_t first = 0u;                               // 0 for the very first MMA of the tile (overwrite D)
+        int g = 0, kb = 0;
+        for (int st = 0; st < stages_per_tile; ++st) {
+          const long long c1 = prof ? clock64() : 0;
           bar_wait(full_bar(stage), phase, p.err_flag, 3);
+          __syncwarp();
           fence_after();
-          const uint32_t sa = smem_base + stage * stage_bytes;
-          const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFFu);
-          const uint64_t b0 = desc_hi | (uint64_t)(((sa + a_region) >> 4) & 0x3FFFu);
-          if (!(p.dbg & 1)) {
+          const long long c2 = prof ? clock64() : 0;
+          const bool el = elect_one();
+          const bool issue = el && !(p.dbg & 1);
+          uint32_t sa = ring_base + stage * stage_bytes;
+          for (int u = 0; u < U; ++u, sa += unit_bytes) {
+            if (issue) {
+              // weight taps of group g are g*G + j; resident tile index (g*G + j) * kb_per_tap + kb
+              const uint32_t sb = p.b_resident ? smem_base + (uint32_t)(g * G * p.kb_per_tap + kb) * b_tile : sa + a_region;
+              const uint64_t b0 = desc_hi | (uint64_t)((sb >> 4) & 0x3FFFu);
+              if (p.a_mode == 1) {
+                const uint32_t sub16 = ((uint32_t)((m0 + (g - 1) * p.Wp - 1) & 7)) * 16u;
+                const uint64_t a0 = desc_a1 | (uint64_t)(((sa + sub16) >> 4) & 0x3FFFu);
 #pragma unroll
-            for (int j = 0; j < G; ++j) {
+                for (int k = 0; k < 2; ++k) umma2_f16(d_tmem, a0 + (uint64_t)(2 * k), b0 + (uint64_t)(2 * k), idesc, first | (uint32_t)k);
+              } else {
+                const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFFu);
 #pragma unroll
-              for (int k = 0; k < kBK / 16; ++k)
-                umma2_f16(d_tmem, a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k), b0 + (uint64_t)(j * (b_tile >> 4) + 2 * k), idesc,
-                          (uint32_t)((it | j | k) != 0));
+                for (int j = 0; j < G; ++j) {
+#pragma unroll
+                  for (int k = 0; k < kBK / 16; ++k)
+                    umma2_f16(d_tmem, a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k), b0 + (uint64_t)(j * b_step + 2 * k), idesc,
+                              first | (uint32_t)(j | k));
+                }
+              }
             }
+            first = 1u;
+            if (++kb == p.kb_per_tap) { kb = 0; ++g; }
           }
-          umma2_commit(empty_bar(stage));   // frees this stage in both CTAs
+          if (el) umma2_commit(empty_bar(stage));   // frees this stage in both CTAs
+          __syncwarp();
+          if (prof) { pc[3] += c2 - c1; pc[4] += clock64() - c2; pc[7] += 1; }
           if (++stage == S) { stage = 0; phase ^= 1u; }
         }
-        umma2_commit(tfull_bar(acc));       // accumulator complete -> both epilogues
-        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+        if (elect_one()) umma2_commit(tfull_bar(acc));       // accumulator complete -> both epilogues
+        __syncwarp();
+        if (++acc == num_acc) { acc = 0; acc_phase ^= 1u; }
+      }
+      if (prof && lane == 0) {
+        pc[5] = clock64() - t_start;
+        for (int i = 2; i < 8; ++i) atomicAdd(p.prof + i, (unsigned long long)pc[i]);
       }
     }
   } else {
@@ -343,28 +451,21 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int half = ew >> 2;
     const int row_in_tile = quarter * 32 + lane;
     const uint32_t lane_addr = ((uint32_t)(quarter * 32)) << 16;
-    const uint32_t stg = staging_base + (uint32_t)(ew * nbuf) * kStageBufBytes;
-    const uint32_t my_row = (uint32_t)lane * 64u;
-    const uint32_t my_xor = ((uint32_t)lane >> 1) & 3u;          // SWIZZLE_64B: 16-byte chunk ^= (row / 2) % 4
     const int hw = p.Hp * p.Wp;
     const int nchunks = p.BN >> 5;
-    uint32_t cid = 0;                                            // chunks processed by this warp -> buffer and barrier phase
     // A tile with a single 32-column chunk would leave half of the epilogue warps idle and make the per-tile
     // latency chain (wait, tcgen05.ld, math, store, arrive) the bound; there the two warps of a quarter take
     // alternate TILES instead of alternate chunks (tile parity = accumulator buffer = `half`).
     const bool split = nchunks == 1;
     const int c_first = split ? 0 : half;
-    auto wait_buffer_free = [&]() {      // all but the newest (nbuf-1) bulk stores of this thread have read their buffer
-      if (nbuf == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
-    };
     int it = 0;
     for (int tile = first_tile; tile < total_tiles; tile += n_clusters, ++it) {
       if (split && (it & 1) != half) continue;
-      const int acc = it & 1;
-      const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
+      const int acc = it % num_acc;
+      const uint32_t acc_phase = (uint32_t)(it / num_acc) & 1u;
+      const long long e0 = prof ? clock64() : 0;
       const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
       const int n0 = (tile % p.num_n_tiles) * p.BN;
-      const int row0 = m0 + quarter * 32;                        // first of this warp's 32 rows
       const int m = m0 + row_in_tile;
       const bool in_range = m < p.P;
       const int img = m / hw;
@@ -374,82 +475,79 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const bool halo = (yy == 0) | (yy == p.Hp - 1) | (xx == 0) | (xx == p.Wp - 1);
       const bool zero_row = halo | !in_range;
 
-      if (!p.head) {
-        uint4* plane_ptr = nullptr;
+      if (p.dbg & 64) {                                          // ablation: no epilogue work at all
+        bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
+        fence_after();
+      } else if (!p.head) {
+        // Thread = output row.  All global traffic of the epilogue is 256-bit per thread (one full 32-byte sector, two per
+        // 32-channel chunk): the residual is read straight into registers BEFORE waiting for the accumulator, so its
+        // latency hides behind the tile's MMAs, and the result is stored straight from registers.  (The earlier TMA
+        // staging - residual box in, result box out, one buffer per warp - serialised a load round trip, a store drain
+        // and a proxy fence per chunk and made the epilogue, not the tensor pipe, the bound of the 3x3 layers.)
+        uint16_t* out_row = static_cast<uint16_t*>(p.out_ptr) + (size_t)m * p.out_pitch + n0;
+        uint16_t* plane_row = nullptr;
         if (p.plane_mode != 0) {
           // padded output pixel (yy, xx) -> plane (yy&1, xx&1), position (yy/2 + 1, xx/2 + 1) of the half-size padded grid
           const int Hq2 = (p.Hp - 2) / 2 + 2, Wq2 = (p.Wp - 2) / 2 + 2;
           const size_t prow = (size_t)((yy & 1) * 2 + (xx & 1)) * (size_t)p.plane_rows +
                               ((size_t)img * Hq2 + (yy >> 1) + 1) * Wq2 + (xx >> 1) + 1;
-          plane_ptr = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.planes) + prow * p.plane_pitch + n0);
+          plane_row = static_cast<uint16_t*>(p.planes) + prow * p.plane_pitch + n0;
         }
-        if (has_res && c_first < nchunks && lane == 0) {         // residual of my first chunk, before the MMAs finish
-          wait_buffer_free();
-          const uint32_t b = cid % nbuf;
-          bar_expect_tx(res_bar(ew, b), kStageBufBytes);
-          tma_load_local(&tmRes, res_bar(ew, b), stg + b * kStageBufBytes, n0 + c_first * 32, row0);
+        uint32_t res[kMaxChunksPerWarp][16];
+        if (has_res && in_range) {
+          const uint16_t* res_row = static_cast<const uint16_t*>(p.res_ptr) + (size_t)m * p.res_pitch + n0;
+#pragma unroll
+          for (int i = 0; i < kMaxChunksPerWarp; ++i) {
+            const int c = c_first + 2 * i;
+            if (c < nchunks) {
+              ldg256(res_row + c * 32, &res[i][0]);
+              ldg256(res_row + c * 32 + 16, &res[i][8]);
+            }
+          }
         }
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
         fence_after();
         const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
-        for (int c = c_first; c < nchunks; c += 2, ++cid) {
-          const uint32_t b = cid % nbuf;
-          const uint32_t buf = stg + b * kStageBufBytes;
-          uint32_t v[32];
-          tmem_load32(t_acc + (uint32_t)(c * 32), v);
-          // bias + LeakyReLU while the residual is still in flight
-          const float4* bias4 = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
-          float f[32];
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 bb = bias4[q];
-            f[4 * q + 0] = __uint_as_float(v[4 * q + 0]) + bb.x;
-            f[4 * q + 1] = __uint_as_float(v[4 * q + 1]) + bb.y;
-            f[4 * q + 2] = __uint_as_float(v[4 * q + 2]) + bb.z;
-            f[4 * q + 3] = __uint_as_float(v[4 * q + 3]) + bb.w;
-          }
-          if (p.leaky) {
+        for (int i = 0; i < kMaxChunksPerWarp; ++i) {
+          const int c = c_first + 2 * i;
+          if (c < nchunks) {
+            uint32_t v[32];
+            tmem_load32(t_acc + (uint32_t)(c * 32), v);
+            const float4* bias4 = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
+            float f[32];
 #pragma unroll
-            for (int e = 0; e < 32; ++e) f[e] = fmaxf(f[e], 0.1f * f[e]);   // == (x > 0 ? x : 0.1x) for every x
-          }
-          if (has_res) {
-            bar_wait(res_bar(ew, b), (cid / nbuf) & 1u, p.err_flag, 5);
-          } else if (p.plane_mode != 2) {
-            if (lane == 0) wait_buffer_free();
-            __syncwarp();
-          }
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {                          // 8 channels = one 16-byte chunk of my row
-            const uint32_t addr = buf + my_row + (((uint32_t)q ^ my_xor) << 4);
-            if (has_res) {
-              uint4 r;
-              lds128(addr, r);
-              const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 rr = unpack_pair<FP16>(rw[e]);
-                f[8 * q + 2 * e] += rr.x;
-                f[8 * q + 2 * e + 1] += rr.y;
-              }
+            for (int q = 0; q < 8; ++q) {
+              const float4 bb = bias4[q];
+              f[4 * q + 0] = __uint_as_float(v[4 * q + 0]) + bb.x;
+              f[4 * q + 1] = __uint_as_float(v[4 * q + 1]) + bb.y;
+              f[4 * q + 2] = __uint_as_float(v[4 * q + 2]) + bb.z;
+              f[4 * q + 3] = __uint_as_float(v[4 * q + 3]) + bb.w;
             }
-            uint4 o;
-            o.x = pack_pair<FP16>(f[8 * q + 0], f[8 * q + 1]);
-            o.y = pack_pair<FP16>(f[8 * q + 2], f[8 * q + 3]);
-            o.z = pack_pair<FP16>(f[8 * q + 4], f[8 * q + 5]);
-            o.w = pack_pair<FP16>(f[8 * q + 6], f[8 * q + 7]);
-            if (zero_row) o = make_uint4(0u, 0u, 0u, 0u);
-            if (p.plane_mode != 2) sts128(addr, o);
-            if (p.plane_mode != 0 && in_range) plane_ptr[(size_t)c * 4 + q] = o;   // 64 B per row and chunk, straight to HBM
-          }
-          if (p.plane_mode != 2) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          __syncwarp();                                          // every lane is done with `buf` (reads and writes)
-          if (lane == 0) {
-            if (!(p.dbg & 4) && p.plane_mode != 2) tma_store_2d(&tmOut, buf, n0 + c * 32, row0);
-            if (has_res && c + 2 < nchunks) {                    // residual of my next chunk
-              wait_buffer_free();
-              const uint32_t b1 = (cid + 1) % nbuf;
-              bar_expect_tx(res_bar(ew, b1), kStageBufBytes);
-              tma_load_local(&tmRes, res_bar(ew, b1), stg + b1 * kStageBufBytes, n0 + (c + 2) * 32, row0);
+            if (p.leaky) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) f[e] = fmaxf(f[e], 0.1f * f[e]);   // == (x > 0 ? x : 0.1x) for every x
+            }
+            uint32_t o[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+              float lo = f[2 * e], hi = f[2 * e + 1];
+              if (has_res) {
+                const float2 rr = unpack_pair<FP16>(res[i][e]);
+                lo += rr.x;
+                hi += rr.y;
+              }
+              o[e] = zero_row ? 0u : pack_pair<FP16>(lo, hi);
+            }
+            if (in_range && !(p.dbg & 4)) {
+              if (p.plane_mode != 2) {
+                stg256(out_row + c * 32, &o[0]);
+                stg256(out_row + c * 32 + 16, &o[8]);
+              }
+              if (p.plane_mode != 0) {
+                stg256(plane_row + c * 32, &o[0]);
+                stg256(plane_row + c * 32 + 16, &o[8]);
+              }
             }
           }
         }
@@ -485,12 +583,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+      if (prof && ew == 0 && lane == 0) { pc[1] += clock64() - e0; pc[2] += 1; }
       // this warp is done reading the accumulator: one arrival per warp on the LEADER's barrier
       fence_before();
       __syncwarp();
       if (lane == 0) bar_arrive_remote(map_to_cta(tempty_bar(acc), 0));
     }
-    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores have left shared memory and landed
+    if (prof && ew == 0 && lane == 0) { atomicAdd(p.prof + 8, (unsigned long long)pc[1]); atomicAdd(p.prof + 9, (unsigned long long)pc[2]); }
   }
 
   // both CTAs must stay resident until the pair's last MMA, commit and remote arrive have landed
@@ -504,40 +603,44 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 }  // namespace
 
-int conv_gemm_stage_bytes(int BN, int G, int a_rows) {
-  return ((a_rows + 7) & ~7) * (int)kRowBytes + G * (BN / 2) * (int)kRowBytes;
+// bytes of one (group, k-block) unit: an A box and, unless the weights are resident, its G weight tiles
+int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident) {
+  return ((a_rows + 7) & ~7) * (int)kRowBytes + (resident ? 0 : G * (BN / 2) * (int)kRowBytes);
 }
 
 static int conv_gemm_fixed_smem(int num_stages, int nbuf) {
-  return kEpiWarps * nbuf * (int)kStageBufBytes + 8 * (2 * num_stages + 4 + kEpiWarps * kMaxStageBufs) + 16 +
+  (void)nbuf;
+  return 8 * (2 * num_stages + 2 * kMaxAcc + kEpiWarps * kMaxStageBufs + 2) + 32 +
          4 * kBiasFloats + 1024 /*alignment*/;
 }
 
 // -> stages (2..8) and staging buffers per epilogue warp (2 when they fit beside >= 3 stages, else 1)
-void conv_gemm_pick_smem(int BN, int G, int a_rows, int* stages, int* nbuf) {
-  const int sb = conv_gemm_stage_bytes(BN, G, a_rows);
-  const int limit = 227 * 1024;
-  int nb = 2;
-  int s = (limit - conv_gemm_fixed_smem(8, nb)) / sb;
-  if (s < 3) {
-    nb = 1;
-    s = (limit - conv_gemm_fixed_smem(8, nb)) / sb;
-  }
+void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int* stages, int* nbuf) {
+  const int sb = units_per_stage * conv_gemm_stage_bytes(BN, G, a_rows, resident_bytes > 0);
+  const int limit = 227 * 1024 - resident_bytes;
+  int s = (limit - conv_gemm_fixed_smem(8, 2)) / sb;
   if (s > 8) s = 8;
   *stages = s;
-  *nbuf = nb;
+  *nbuf = 2;      // kept for the plan's bookkeeping: the epilogue no longer stages through shared memory
 }
 
 int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
                      const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
                      cudaStream_t stream) {
   if (p.BN % 32 != 0 || p.BN < 32 || p.BN > 256 || p.num_stages < 2 || p.num_stages > 8 || (G != 1 && G != 3) ||
-      (p.nbuf != 1 && p.nbuf != 2) || p.num_n_tiles * p.BN > kBiasFloats) {
+      (p.nbuf != 1 && p.nbuf != 2) || p.num_n_tiles * p.BN > kBiasFloats || p.units_per_stage < 1 ||
+      (p.n_groups * p.kb_per_tap) % p.units_per_stage != 0) {
     set_error("conv_gemm: unsupported tile BN=%d G=%d stages=%d nbuf=%d n_tiles=%d", p.BN, G, p.num_stages, p.nbuf,
               p.num_n_tiles);
     return AY_EINVAL;
   }
-  const int smem = p.num_stages * conv_gemm_stage_bytes(p.BN, G, p.a_rows) + conv_gemm_fixed_smem(p.num_stages, p.nbuf);
+  const int smem = (p.b_resident ? p.b_res_tiles * (p.BN / 2) * (int)kRowBytes : 0) +
+                   p.num_stages * p.units_per_stage * conv_gemm_stage_bytes(p.BN, G, p.a_rows, p.b_resident) +
+                   conv_gemm_fixed_smem(p.num_stages, p.nbuf);
+  if (smem > 227 * 1024 || (p.b_resident && p.num_n_tiles != 1)) {
+    set_error("conv_gemm: shared memory plan does not fit (%d bytes, resident=%d)", smem, p.b_resident);
+    return AY_EINVAL;
+  }
   const int total = p.num_m_tiles * p.num_n_tiles;
   const int pairs = num_sms / 2;
   const int grid = 2 * (total < pairs ? total : pairs);

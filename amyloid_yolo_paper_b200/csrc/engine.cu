@@ -87,6 +87,18 @@ uint16_t to16(float v, int is_fp16) {
   return u;
 }
 
+float from16(uint16_t u, int is_fp16) {
+  if (is_fp16) {
+    __half h;
+    memcpy(&h, &u, 2);
+    return __half2float(h);
+  }
+  uint32_t w = (uint32_t)u << 16;
+  float f;
+  memcpy(&f, &w, 4);
+  return f;
+}
+
 struct Layer {
   ay_layer_desc d;
   int C = 0, H = 0, W = 0;          // logical output shape
@@ -95,6 +107,8 @@ struct Layer {
   // convolution
   int cin = 0, cin_p = 0, cin_k = 0, cout_rows = 0, ktot = 0;   // cin_p: channels stored (x32); cin_k: K per tap (x64)
   int BN = 0, G = 1, a_rows = 128, stages = 0, nbuf = 1;
+  int units_per_stage = 1;          // (group, k-block) units per pipeline stage
+  int b_resident = 0;               // weights stay in shared memory for the whole launch (single N tile, small K)
   int impl = 0;                     // 0 none, 1 tcgen05 gemm
   bool first = false;               // 3-channel first layer: GEMM over the staged 8-channel input x8
   void* x8 = nullptr;               // [B, S+2, S+2, 8] 16-bit (first layer only)
@@ -141,6 +155,10 @@ struct ay_ctx {
   int idx_src_h = -1, idx_src_w = -1;
   std::vector<void*> allocs;
   int launches = 0;
+  // per-layer timing (ay_forward_profile): one event before every cfg block and one after the last
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_events;
+  unsigned long long* prof_counters = nullptr;   // [n_layers][16], device
   // post-processing scratch
   void* nms_scratch = nullptr; size_t nms_bytes = 0;
   void* merge_scratch = nullptr; size_t merge_bytes = 0;
@@ -248,6 +266,8 @@ extern "C" int ay_destroy(ay_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   ay::free_network(ctx);
+  for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
+  if (ctx->prof_counters) cudaFree(ctx->prof_counters);
   if (ctx->nms_scratch) cudaFree(ctx->nms_scratch);
   if (ctx->merge_scratch) cudaFree(ctx->merge_scratch);
   if (ctx->err_flag) cudaFree(ctx->err_flag);
@@ -471,12 +491,12 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     Layer& L = Ls[i];
     if (L.d.type != AY_CONV) continue;
     if (L.first) {
-      // First layer as a GEMM with K = 3 (kh) x 64: the A row of output pixel (y, x) and tap row kh is the 24
-      // contiguous elements of the three 8-channel pixels (y+kh-1, x-1..x+1) of x8.  The tensor map declares 24
-      // inner elements and a row stride of ONE pixel (16 B), i.e. overlapping rows; elements 24..63 of the 64-wide
-      // box are out of bounds and zero-filled.  Weight column kh*64 + kw*8 + c.
+      // First layer as a GEMM with K = 3 (kh) x 64: x8 holds 8 channels (3 used) per padded pixel, 16 bytes, so the
+      // three pixels (y+kh-1, x-1..x+1) of a filter row are 24 contiguous elements.  The kernel loads 144 consecutive
+      // pixels per filter row and reads them as overlapping unswizzled core matrices (conv_gemm_sm100.cu, a_mode 1).
+      // Weight column kh*64 + kw*8 + c.
       AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.w32), sizeof(float) * L.C * 27, true));   // reference path
-      const long long rows8 = ay::padded_rows(max_batch, ph0, pw0);
+      const long long rows8 = (ay::padded_rows(max_batch, ph0, pw0) + 7) / 8 * 8;
       AY_TRY(ay::dev_alloc(ctx, &L.x8, (size_t)rows8 * 8 * 2, true));
       L.cin_p = 8;
       L.cin_k = 64;
@@ -496,8 +516,37 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     else L.BN = (cout_p % 256 == 0) ? 256 : (cout_p % 128 == 0) ? 128 : (cout_p % 64 == 0) ? 64 : 32;
     L.cout_rows = ay::round_up(cout_p, L.BN);
     L.G = (L.d.size == 3 && L.d.stride == 1 && !L.first) ? 3 : 1;
-    L.a_rows = L.G == 3 ? 130 : 128;
-    ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, &L.stages, &L.nbuf);
+    L.a_rows = L.first ? 18 : L.G == 3 ? 130 : 128;
+    {
+      // resident weights when this CTA's half of the matrix leaves room for the A ring;
+      // units per stage: the largest divisor of the tile's unit count that keeps a stage <= 56 KB and >= 3 stages
+      const int res_bytes = (L.BN / 2) * L.ktot * 2;
+      const int n_groups = L.first ? 3 : L.d.size == 1 ? 1 : L.d.stride == 1 ? 3 : 9;
+      const int units = n_groups * (L.cin_k / 64);
+      const bool try_res = L.cout_rows == L.BN && res_bytes <= 96 * 1024 && !getenv("AY_NO_RESIDENT");
+      L.units_per_stage = 1;
+      for (int pass = try_res ? 0 : 1; pass < 2 && L.stages == 0; ++pass) {
+        const int rb = pass == 0 ? res_bytes : 0;
+        const int unit_bytes = ay::conv_gemm_stage_bytes(L.BN, L.G, L.a_rows, rb > 0);
+        int best_u = 0, best_st = 0, best_nb = 0;
+        for (int u = 1; u <= units; ++u) {
+          if (units % u != 0 || (u > 1 && (u * unit_bytes > 56 * 1024 || getenv("AY_ONE_UNIT")))) continue;
+          int st = 0, nb = 0;
+          ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, rb, u, &st, &nb);
+          if (st >= 3 && (u == 1 || nb == 2)) { best_u = u; best_st = st; best_nb = nb; }
+        }
+        if (best_u == 0 && pass == 1) {
+          best_u = 1;
+          ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, 0, 1, &best_st, &best_nb);
+        }
+        if (best_u > 0 && (pass == 1 || best_st >= 3)) {
+          L.b_resident = pass == 0;
+          L.units_per_stage = best_u;
+          L.stages = best_st;
+          L.nbuf = best_nb;
+        }
+      }
+    }
     if (L.stages < 2) { set_error("layer %d: tile does not fit in shared memory", i); return AY_EINVAL; }
     AY_TRY(ay::dev_alloc(ctx, &L.w16, (size_t)L.cout_rows * L.ktot * 2, true));
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.cout_rows, true));
@@ -505,7 +554,9 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     // A boxes are always 64 channels wide; when the tensor stores only 32 (cin_p = 32) the upper half of the
     // box lies outside the tensor and the TMA zero-fills it (the matching weight columns are zero as well)
     if (L.first) {
-      AY_TRY(ay::make_map_2d(&L.tmA, L.x8, 24, ay::padded_rows(max_batch, ph0, pw0), 8, 64, L.a_rows, ctx->is_fp16));
+      // x8 viewed as rows of 8 pixels x 8 channels (128 contiguous bytes): an 18-row box is 144 consecutive pixels
+      AY_TRY(ay::make_map_2d(&L.tmA, L.x8, 64, (ay::padded_rows(max_batch, ph0, pw0) + 7) / 8, 64, 64, L.a_rows,
+                             ctx->is_fp16, /*swizzle=*/false));
     } else if (L.d.stride == 2) {
       AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, 64, L.a_rows, ctx->is_fp16));
     } else {
@@ -547,8 +598,12 @@ extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const flo
     for (int o = 0; o < cout; ++o)
       for (int c = 0; c < 3; ++c)
         for (int t = 0; t < 9; ++t) {
-          r[(size_t)o * 27 + t * 3 + c] = w[((size_t)o * 3 + c) * 9 + t];
-          r16[(size_t)o * L.ktot + (t / 3) * 64 + (t % 3) * 8 + c] = ay::to16(w[((size_t)o * 3 + c) * 9 + t], ctx->is_fp16);
+          // the CUDA-core reference of this layer uses the SAME rounded operands as the tensor-core path
+          r[(size_t)o * 27 + t * 3 + c] =
+              ay::from16(ay::to16((float)((double)w[((size_t)o * 3 + c) * 9 + t] / 255.0), ctx->is_fp16), ctx->is_fp16);
+          // the staged input holds pixel values 0..255 (exact in 16 bits): ToTensor's 1/255 lives in the weights
+          r16[(size_t)o * L.ktot + (t / 3) * 64 + (t % 3) * 8 + c] =
+              ay::to16((float)((double)w[((size_t)o * 3 + c) * 9 + t] / 255.0), ctx->is_fp16);
         }
     std::vector<float> b(L.cout_rows, 0.f);
     memcpy(b.data(), bias, sizeof(float) * cout);
@@ -704,11 +759,16 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
         q.b_tap0[kh * 3 + kw] = kh * 3 + kw;
       }
   }
-  q.BN = L.BN; q.num_stages = L.stages; q.nbuf = L.nbuf;
+  q.BN = L.BN; q.num_stages = L.stages; q.nbuf = L.nbuf; q.units_per_stage = L.units_per_stage;
+  q.num_acc = std::min(16, 512 / L.BN);
+  q.b_resident = L.b_resident;
+  q.b_res_tiles = L.ktot / 64;
+  q.a_mode = L.first ? 1 : 0;
   q.dbg = ctx->dbg;
   q.Hp = Hq; q.Wp = Wq;
   q.bias = L.bias; q.leaky = L.d.leaky;
   q.err_flag = ctx->err_flag;
+  q.prof = (ctx->profiling && ctx->prof_counters) ? ctx->prof_counters + (size_t)i * 16 : nullptr;
   if (L.is_head) {
     q.head = 1;
     q.dec_out = dec_out; q.dec_rows_total = ctx->dec_rows; q.dec_row_off = Y->dec_row_off;
@@ -722,6 +782,8 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   } else {
     q.has_res = res ? 1 : 0;
     q.cout = L.C;
+    q.out_ptr = target->ptr; q.out_pitch = target->pitch;
+    q.res_ptr = res ? res->ptr : nullptr; q.res_pitch = res ? res->pitch : 0;
     if (L.plane_consumer >= 0) {
       const Layer& Cn = Ls[L.plane_consumer];
       q.plane_mode = L.plane_mode;
@@ -770,6 +832,7 @@ extern "C" int ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch
   std::vector<Layer>& Ls = ctx->layers;
   for (int i = 0; i < (int)Ls.size(); ++i) {
     Layer& L = Ls[i];
+    if (ctx->profiling) AY_CUDA(cudaEventRecord(ctx->prof_events[i], st));
     switch (L.d.type) {
       case AY_CONV:
         AY_TRY(run_conv(ctx, i, input, in_kind, batch, src_h, src_w, out_decoded, st));
@@ -808,6 +871,48 @@ extern "C" int ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch
         break;
     }
   }
+  if (ctx->profiling) AY_CUDA(cudaEventRecord(ctx->prof_events[Ls.size()], st));
+  return AY_OK;
+}
+
+extern "C" int ay_debug_set(ay_ctx* ctx, int bits) {
+  if (!ctx) { set_error("null context"); return AY_EINVAL; }
+  ctx->dbg = bits;
+  return AY_OK;
+}
+
+extern "C" int ay_forward_profile(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                                  float* out_decoded, void* stream, float* ms_per_layer_h, int n_layers) {
+  AY_ENTER(ctx);
+  if (!ms_per_layer_h || n_layers != (int)ctx->layers.size()) {
+    set_error("ay_forward_profile: expected %d layer slots", (int)ctx->layers.size());
+    return AY_EINVAL;
+  }
+  while (ctx->prof_events.size() < ctx->layers.size() + 1) {
+    cudaEvent_t e;
+    AY_CUDA(cudaEventCreate(&e));
+    ctx->prof_events.push_back(e);
+  }
+  if (!ctx->prof_counters) AY_CUDA(cudaMalloc(&ctx->prof_counters, sizeof(unsigned long long) * 16 * ctx->layers.size()));
+  AY_CUDA(cudaMemsetAsync(ctx->prof_counters, 0, sizeof(unsigned long long) * 16 * ctx->layers.size(),
+                          static_cast<cudaStream_t>(stream)));
+  ctx->profiling = true;
+  const int rc = ay_forward(ctx, input, in_kind, batch, src_h, src_w, out_decoded, stream);
+  ctx->profiling = false;
+  if (rc != AY_OK) return rc;
+  AY_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  for (int i = 0; i < n_layers; ++i)
+    AY_CUDA(cudaEventElapsedTime(&ms_per_layer_h[i], ctx->prof_events[i], ctx->prof_events[i + 1]));
+  return AY_OK;
+}
+
+extern "C" int ay_debug_counters(ay_ctx* ctx, unsigned long long* out_h, int n_layers) {
+  AY_ENTER(ctx);
+  if (!out_h || n_layers != (int)ctx->layers.size() || !ctx->prof_counters) {
+    set_error("ay_debug_counters: call ay_forward_profile first");
+    return AY_ESTATE;
+  }
+  AY_CUDA(cudaMemcpy(out_h, ctx->prof_counters, sizeof(unsigned long long) * 16 * n_layers, cudaMemcpyDeviceToHost));
   return AY_OK;
 }
 

@@ -44,13 +44,13 @@ def synthetic_tiles_fast(batch, size=1536, seed=0xA11CE, first_tile=0):
     return rng.integers(0, 256, size=(batch, size, size, 3), dtype=np.uint8)
 
 
-def synthetic_state_dict(model, seed=0, conf_bias=None):
+def synthetic_state_dict(model, seed=0, conf_bias=None, wh_gain=None):
     """Fill ``model`` (a Darknet module) with the seeded synthetic checkpoint of
     SURVEY.md §8c and return its state_dict: conv N(0,0.02) scaled up so that
     activations neither die nor explode over 75 layers, BN gamma N(1,0.02),
     beta small, running stats randomised so BN folding is exercised, head
     objectness biases set from ``conf_bias`` so that a controllable fraction of
-    rows clears the confidence threshold."""
+    rows clears the confidence threshold.  ``wh_gain`` (optional) shrinks the box-size outputs."""
     g = torch.Generator().manual_seed(seed)
     sd = model.state_dict()
     defs = model.module_defs
@@ -79,11 +79,23 @@ def synthetic_state_dict(model, seed=0, conf_bias=None):
         elif leaf == "num_batches_tracked":
             t.fill_(105)
     if conf_bias is not None:
+        head = 0                                     # heads in cfg order (grids 13, 26, 52 for yolov3-custom)
         for key, t in sd.items():
             if "conv_" in key and key.endswith(".bias"):
+                bias = conf_bias[min(head, len(conf_bias) - 1)] if isinstance(conf_bias, (tuple, list)) else conf_bias
+                head += 1
                 per_anchor = t.numel() // 3
                 for a in range(3):
-                    t[a * per_anchor + 4] = conf_bias
+                    t[a * per_anchor + 4] = bias
+    if wh_gain is not None:
+        # box-size channels (tw, th) of the heads scaled down: sizes stay within a factor ~2 of the anchors, like a
+        # trained detector's, instead of exp(N(0,1.5)) * anchor (mergeDetections enumerates box pixels on the CPU path)
+        for key, t in sd.items():
+            layer = int(key.split(".")[1])
+            if "conv_" in key and layer + 1 < len(defs) and defs[layer + 1]["type"] == "yolo":
+                per_anchor = t.shape[0] // 3
+                for a in range(3):
+                    t[a * per_anchor + 2:a * per_anchor + 4] *= wh_gain
     model.load_state_dict(sd)
     return model.state_dict()
 

@@ -116,6 +116,15 @@ int  ay_check(ay_ctx* ctx, void* stream);
 /* Plain CUDA-core direct convolution over the same padded NHWC buffers (no tensor
  * cores); used by tests to cross-check the tcgen05 kernel at full size on the GPU.  */
 int  ay_net_use_reference_conv(ay_ctx* ctx, int enable);
+/* Profiling: ay_forward with a CUDA event before every cfg block; synchronises `stream` and
+ * writes the milliseconds each block's kernels took into ms_per_layer_h[n_layers].   */
+int  ay_forward_profile(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                        float* out_decoded, void* stream, float* ms_per_layer_h, int n_layers);
+/* Ablation switches of the convolution kernel (tools/layer_times.py): 1 no MMA, 2 no operand
+ * loads, 4 no output stores, 8 no residual.  Results are meaningless while any bit is set. */
+int  ay_debug_set(ay_ctx* ctx, int bits);
+/* Cycle counters of the last ay_forward_profile: 16 per layer (meaning: conv_gemm_sm100.cu). */
+int  ay_debug_counters(ay_ctx* ctx, unsigned long long* out_h, int n_layers);
 
 #ifdef __cplusplus
 }

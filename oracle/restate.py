@@ -127,8 +127,13 @@ def darknet_forward(blocks, state, x, emulate_bf16=False, return_layers=False, r
                     w = w * s.view(-1, 1, 1, 1)
                     cb = b - mu * s
                 is_head = defs[i + 1]["type"] == "yolo" if i + 1 < len(defs) else False
-                # the engine's first layer (Cin=3) runs in fp32 on fp32 weights and input
-                wq = w if (i == 0 and w.shape[1] < 8) else q(w)
+                # the engine's first layer (Cin=3) contracts pixel values 0..255 (exact in bf16 for uint8 sources)
+                # with bf16(w / 255): ToTensor's scale is folded into the weights
+                if i == 0 and w.shape[1] < 8:
+                    x = q(x * 255.0)
+                    wq = q((w.double() / 255.0).float())
+                else:
+                    wq = q(w)
                 fused_add = (not is_head) and i + 1 < len(defs) and defs[i + 1]["type"] == "shortcut"
                 x = F.conv2d(x, wq, None, int(d["stride"]), (k - 1) // 2) + cb.view(1, -1, 1, 1)
                 if d["activation"] == "leaky":
