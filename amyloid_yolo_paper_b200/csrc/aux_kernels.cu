@@ -250,8 +250,9 @@ __global__ void dump_nchw_kernel(const void* __restrict__ in, int in_pitch, int 
 }
 
 // same, reading the parity planes a stride-2 consumer uses (a producer may store only those)
+// packed != 0: two ROW-parity planes whose rows hold the column-parity pair side by side (2 x pitch channels)
 __global__ void dump_planes_nchw_kernel(const void* __restrict__ planes, long long plane_rows, int pitch, int C, int batch,
-                                        int H, int W, int is_fp16, float* __restrict__ out) {
+                                        int H, int W, int is_fp16, int packed, float* __restrict__ out) {
   const long long total = (long long)batch * C * H * W;
   const int Hq = H / 2 + 2, Wq = W / 2 + 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -263,8 +264,13 @@ __global__ void dump_planes_nchw_kernel(const void* __restrict__ planes, long lo
     const int c = (int)(r % C);
     const int n = (int)(r / C);
     const int yp = y + 1, xp = x + 1;
-    const size_t row = (size_t)((yp & 1) * 2 + (xp & 1)) * plane_rows + ((size_t)n * Hq + (yp >> 1) + 1) * Wq + (xp >> 1) + 1;
-    out[i] = ld16(planes, row * pitch + c, is_fp16);
+    const size_t pos = ((size_t)n * Hq + (yp >> 1) + 1) * Wq + (xp >> 1) + 1;
+    if (packed) {
+      out[i] = ld16(planes, ((size_t)(yp & 1) * plane_rows + pos) * (2 * pitch) + (xp & 1) * pitch + c, is_fp16);
+    } else {
+      const size_t row = (size_t)((yp & 1) * 2 + (xp & 1)) * plane_rows + pos;
+      out[i] = ld16(planes, row * pitch + c, is_fp16);
+    }
   }
 }
 
@@ -408,9 +414,9 @@ int launch_dump_nchw(const void* in, int in_pitch, int C, int batch, int H, int 
 }
 
 int launch_dump_planes_nchw(const void* planes, long long plane_rows, int pitch, int C, int batch, int H, int W,
-                            int is_fp16, float* out, cudaStream_t s) {
+                            int is_fp16, int packed, float* out, cudaStream_t s) {
   dump_planes_nchw_kernel<<<grid_for((long long)batch * C * H * W), 256, 0, s>>>(planes, plane_rows, pitch, C, batch, H, W,
-                                                                               is_fp16, out);
+                                                                               is_fp16, packed, out);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

@@ -45,7 +45,7 @@ struct ActView {
 // taps that read it (G = 3: the kw taps of one kh of a 3x3/stride-1 layer; G = 1 otherwise).
 struct ConvGemmParams {
   int P;                 // output rows to compute: batch * (H+2) * (W+2)
-  int num_m_tiles;       // ceil(P / 256): one tile per CTA pair
+  int num_m_tiles;       // ceil(P / (256 * m_batch)): one tile per CTA pair
   int num_n_tiles;       // Cout_padded / BN
   int n_groups;          // A boxes per k-block
   int kb_per_tap;        // ceil(Cin / 64)
@@ -54,6 +54,7 @@ struct ConvGemmParams {
   int a_rows;            // rows of the A box (128, or 130 with tap reuse)
   int BN;                // N of the pair tile (each CTA loads BN/2 weight rows)
   int num_stages;
+  int m_batch;           // 256-row blocks per tile (row batching; > 1 only with BN = 32, no residual, not a head)
   int units_per_stage;   // (group, k-block) units loaded and consumed per pipeline stage (divides n_groups*kb_per_tap)
   int num_acc;           // TMEM accumulator buffers (512 / BN, at most 16)
   int b_resident;        // this CTA's half of ALL weight tiles stays in shared memory for the whole launch
@@ -73,6 +74,7 @@ struct ConvGemmParams {
   void* planes;
   long long plane_rows;
   int plane_pitch;
+  int plane_packed;      // 32-channel producer: the column-parity pair shares one 64-channel row of a ROW-parity plane
   // fused YOLO decode (head convolutions)
   int head;
   float* dec_out;        // [B, dec_rows_total, dec_cols]
@@ -111,7 +113,7 @@ int launch_copy_channels(const void* in, int in_pitch, int Cp, long long rows, v
 int launch_dump_nchw(const void* in, int in_pitch, int C, int batch, int H, int W, int is_fp16,
                      float* out, cudaStream_t s);
 int launch_dump_planes_nchw(const void* planes, long long plane_rows, int pitch, int C, int batch, int H, int W,
-                            int is_fp16, float* out, cudaStream_t s);
+                            int is_fp16, int packed, float* out, cudaStream_t s);
 struct RefConvParams {
   const void* in; int in_pitch; int Cin_p; int Cin_k; int H, W;   // input (unpadded H,W); Cin_k: weight columns per tap
   const void* w; int ktot;                                     // [Cout_p][taps*Cin_k] 16-bit

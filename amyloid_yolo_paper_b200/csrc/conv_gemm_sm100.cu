@@ -229,6 +229,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t res_bytes = p.b_resident ? (uint32_t)p.b_res_tiles * b_tile : 0u;
   const uint32_t ring_base = smem_base + res_bytes;
   const int U = p.units_per_stage;                    // (group, k-block) units per pipeline stage
+  // row batching (small-N layers): a tile is R consecutive 256-row blocks, each with its own BN accumulator columns,
+  // loaded, multiplied and handed over together - one barrier round per R blocks instead of one per block
+  const int R = p.m_batch;
+  const int tile_rows = 2 * kRowsPerCta * R;
+  const int acc_cols = p.BN * R;
   const uint32_t unit_bytes = a_region + (p.b_resident ? 0u : G * b_tile);
   const uint32_t stage_bytes = (uint32_t)U * unit_bytes;
   const uint32_t tx_bytes = (uint32_t)U * ((uint32_t)p.a_rows * kRowBytes + (p.b_resident ? 0u : G * b_tile));   // one CTA's loads per stage
@@ -275,7 +280,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int a = 0; a < kMaxAcc; ++a) {
       bar_init(tfull_bar(a), 1);                // tcgen05.commit multicast
       // leader's copy: the epilogue warps of both CTAs that work on a tile (all 8, or 4 when BN = 32: see `split`)
-      bar_init(tempty_bar(a), p.BN == 32 ? kEpiWarps : 2 * kEpiWarps);
+      bar_init(tempty_bar(a), acc_cols == 32 ? kEpiWarps : 2 * kEpiWarps);
     }
     for (int w = 0; w < kEpiWarps; ++w)
       for (int b = 0; b < kMaxStageBufs; ++b) bar_init(res_bar(w, b), 1);   // residual TMA loads, per epilogue warp
@@ -323,9 +328,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       __syncwarp();
       for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
-        const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
+        const int m0 = (tile / p.num_n_tiles) * tile_rows + (int)rank * kRowsPerCta * R;   // this CTA's rows are contiguous
         const int n0 = (tile % p.num_n_tiles) * p.BN + (int)rank * (p.BN / 2);
-        // a pipeline stage holds U consecutive (group, k-block) units: one barrier round trip per stage
+        // a pipeline stage holds U consecutive (row block, group, k-block) units: one barrier round trip per stage
         int g = 0, kb = 0;
         for (int st = 0; st < stages_per_tile; ++st) {
           const long long c0 = prof ? clock64() : 0;
@@ -390,8 +395,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         __syncwarp();
         fence_after();
         if (prof) { pc[2] += clock64() - c0; pc[6] += 1; }
-        const uint32_t d_tmem = (uint32_t)(acc * p.BN);    // tmem_base == 0 (checked after the allocation)
-        const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta);
+        const uint32_t d_tmem = (uint32_t)(acc * acc_cols);      // tmem_base == 0 (checked after the allocation)
+        const int m0 = (tile / p.num_n_tiles) * tile_rows;       // (m0 & 7) == 0, also for the peer CTA's first row
         // groups and k-blocks as nested loops with running addresses: the issuing warp has nothing to hide latency
         // with, so every dependent scalar instruction between two barriers (a division, an indexed constant load)
         // shows up in the layer time
@@ -412,10 +417,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const uint32_t sb = p.b_resident ? smem_base + (uint32_t)(g * G * p.kb_per_tap + kb) * b_tile : sa + a_region;
               const uint64_t b0 = desc_hi | (uint64_t)((sb >> 4) & 0x3FFFu);
               if (p.a_mode == 1) {
+                // the box holds this CTA's 128*R consecutive rows (+ shift and taps): row block rb starts rb*128 pixels in
+                // and accumulates into its own BN columns
                 const uint32_t sub16 = ((uint32_t)((m0 + (g - 1) * p.Wp - 1) & 7)) * 16u;
                 const uint64_t a0 = desc_a1 | (uint64_t)(((sa + sub16) >> 4) & 0x3FFFu);
+                const uint32_t acc_flag = g != 0 ? 1u : 0u;
+#pragma unroll 4
+                for (int rb = 0; rb < R; ++rb) {
 #pragma unroll
-                for (int k = 0; k < 2; ++k) umma2_f16(d_tmem, a0 + (uint64_t)(2 * k), b0 + (uint64_t)(2 * k), idesc, first | (uint32_t)k);
+                  for (int k = 0; k < 2; ++k)
+                    umma2_f16(d_tmem + (uint32_t)(rb * p.BN), a0 + (uint64_t)(rb * kRowsPerCta + 2 * k), b0 + (uint64_t)(2 * k), idesc,
+                              acc_flag | (uint32_t)k);
+                }
               } else {
                 const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFFu);
 #pragma unroll
@@ -452,7 +465,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int row_in_tile = quarter * 32 + lane;
     const uint32_t lane_addr = ((uint32_t)(quarter * 32)) << 16;
     const int hw = p.Hp * p.Wp;
-    const int nchunks = p.BN >> 5;
+    const int nchunks = (p.BN >> 5) * R;
     // A tile with a single 32-column chunk would leave half of the epilogue warps idle and make the per-tile
     // latency chain (wait, tcgen05.ld, math, store, arrive) the bound; there the two warps of a quarter take
     // alternate TILES instead of alternate chunks (tile parity = accumulator buffer = `half`).
@@ -464,7 +477,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int acc = it % num_acc;
       const uint32_t acc_phase = (uint32_t)(it / num_acc) & 1u;
       const long long e0 = prof ? clock64() : 0;
-      const int m0 = (tile / p.num_n_tiles) * (2 * kRowsPerCta) + (int)rank * kRowsPerCta;
+      const int m0 = (tile / p.num_n_tiles) * tile_rows + (int)rank * kRowsPerCta * R;
       const int n0 = (tile % p.num_n_tiles) * p.BN;
       const int m = m0 + row_in_tile;
       const bool in_range = m < p.P;
@@ -473,7 +486,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int yy = pix / p.Wp;
       const int xx = pix - yy * p.Wp;
       const bool halo = (yy == 0) | (yy == p.Hp - 1) | (xx == 0) | (xx == p.Wp - 1);
-      const bool zero_row = halo | !in_range;
 
       if (p.dbg & 64) {                                          // ablation: no epilogue work at all
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
@@ -484,14 +496,40 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // latency hides behind the tile's MMAs, and the result is stored straight from registers.  (The earlier TMA
         // staging - residual box in, result box out, one buffer per warp - serialised a load round trip, a store drain
         // and a proxy fence per chunk and made the epilogue, not the tensor pipe, the bound of the 3x3 layers.)
-        uint16_t* out_row = static_cast<uint16_t*>(p.out_ptr) + (size_t)m * p.out_pitch + n0;
-        uint16_t* plane_row = nullptr;
-        if (p.plane_mode != 0) {
-          // padded output pixel (yy, xx) -> plane (yy&1, xx&1), position (yy/2 + 1, xx/2 + 1) of the half-size padded grid
-          const int Hq2 = (p.Hp - 2) / 2 + 2, Wq2 = (p.Wp - 2) / 2 + 2;
-          const size_t prow = (size_t)((yy & 1) * 2 + (xx & 1)) * (size_t)p.plane_rows +
-                              ((size_t)img * Hq2 + (yy >> 1) + 1) * Wq2 + (xx >> 1) + 1;
-          plane_row = static_cast<uint16_t*>(p.planes) + prow * p.plane_pitch + n0;
+        // Chunk c of a tile is 32 accumulator columns: channels c*32.. of the tile's rows, or - for row-batched tiles
+        // (m_batch > 1, BN = 32) - all 32 channels of the rows of sub-block c.
+        struct RowTarget { bool store, zero; uint16_t* out; uint16_t* plane; };
+        auto row_target = [&](int mr, int image, int py, int px, bool is_halo) {
+          RowTarget t;
+          t.store = mr < p.P;
+          t.zero = is_halo | !t.store;
+          t.out = static_cast<uint16_t*>(p.out_ptr) + (size_t)mr * p.out_pitch + n0;
+          t.plane = nullptr;
+          if (p.plane_mode != 0) {
+            // padded output pixel (py, px) -> plane (py&1, px&1), position (py/2 + 1, px/2 + 1) of the half-size padded grid
+            const int Hq2 = (p.Hp - 2) / 2 + 2, Wq2 = (p.Wp - 2) / 2 + 2;
+            const size_t pos = ((size_t)image * Hq2 + (py >> 1) + 1) * Wq2 + (px >> 1) + 1;
+            if (p.plane_packed) {
+              // row-parity plane, 2 x pitch channels per row: [pixel with even padded x | pixel with odd padded x]
+              t.plane = static_cast<uint16_t*>(p.planes) + ((size_t)(py & 1) * (size_t)p.plane_rows + pos) * (2 * p.plane_pitch) +
+                        (px & 1) * p.plane_pitch + n0;
+            } else {
+              const size_t prow = (size_t)((py & 1) * 2 + (px & 1)) * (size_t)p.plane_rows + pos;
+              t.plane = static_cast<uint16_t*>(p.planes) + prow * p.plane_pitch + n0;
+            }
+          }
+          return t;
+        };
+        const RowTarget t0 = row_target(m, img, yy, xx, halo);
+        if (has_res) {
+          // pull the residual rows of the tile two rounds ahead into L2
+          const int nt = tile + 2 * n_clusters;
+          const long long mp = (long long)(nt / p.num_n_tiles) * tile_rows + (int)rank * kRowsPerCta * R + row_in_tile;
+          if (nt < total_tiles && mp < p.P) {
+            const uint16_t* pf = static_cast<const uint16_t*>(p.res_ptr) + (size_t)mp * p.res_pitch + (nt % p.num_n_tiles) * p.BN;
+            for (int l = half; l < (p.BN >> 6); l += 2)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + l * 64) : "memory");
+          }
         }
         uint32_t res[kMaxChunksPerWarp][16];
         if (has_res && in_range) {
@@ -507,14 +545,24 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
         fence_after();
-        const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
+        const uint32_t t_acc = tmem_base + (uint32_t)(acc * acc_cols) + lane_addr;
 #pragma unroll
         for (int i = 0; i < kMaxChunksPerWarp; ++i) {
           const int c = c_first + 2 * i;
           if (c < nchunks) {
             uint32_t v[32];
             tmem_load32(t_acc + (uint32_t)(c * 32), v);
-            const float4* bias4 = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
+            RowTarget t = t0;
+            int ch = c * 32;
+            if (R > 1) {                                         // sub-block c of a row-batched tile: 128 rows further per c
+              const int mr = m + c * kRowsPerCta;
+              int px = xx + c * kRowsPerCta, py = yy, image = img;   // (no divisions: c * 128 < 4 rows of the image)
+              while (px >= p.Wp) { px -= p.Wp; ++py; }
+              if (py >= p.Hp) { py -= p.Hp; ++image; }
+              t = row_target(mr, image, py, px, (py == 0) | (py == p.Hp - 1) | (px == 0) | (px == p.Wp - 1));
+              ch = 0;
+            }
+            const float4* bias4 = reinterpret_cast<const float4*>(s_bias + n0 + ch);
             float f[32];
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
@@ -537,16 +585,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 lo += rr.x;
                 hi += rr.y;
               }
-              o[e] = zero_row ? 0u : pack_pair<FP16>(lo, hi);
+              o[e] = t.zero ? 0u : pack_pair<FP16>(lo, hi);
             }
-            if (in_range && !(p.dbg & 4)) {
+            if (t.store && !(p.dbg & 4)) {
               if (p.plane_mode != 2) {
-                stg256(out_row + c * 32, &o[0]);
-                stg256(out_row + c * 32 + 16, &o[8]);
+                stg256(t.out + ch, &o[0]);
+                stg256(t.out + ch + 16, &o[8]);
               }
               if (p.plane_mode != 0) {
-                stg256(plane_row + c * 32, &o[0]);
-                stg256(plane_row + c * 32 + 16, &o[8]);
+                stg256(t.plane + ch, &o[0]);
+                stg256(t.plane + ch + 16, &o[8]);
               }
             }
           }
@@ -555,7 +603,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // fused YOLOLayer decode (models.py:137-169): channel ch = a*(5+C) + f
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
         fence_after();
-        const uint32_t t_acc = tmem_base + (uint32_t)(acc * p.BN) + lane_addr;
+        const uint32_t t_acc = tmem_base + (uint32_t)(acc * acc_cols) + lane_addr;
         const int Gd = p.Wp - 2;
         const int gx = xx - 1, gy = yy - 1;
         float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols +
@@ -627,9 +675,10 @@ void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int unit
 int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
                      const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
                      cudaStream_t stream) {
-  if (p.BN % 32 != 0 || p.BN < 32 || p.BN > 256 || p.num_stages < 2 || p.num_stages > 8 || (G != 1 && G != 3) ||
+  if (p.BN % 32 != 0 || p.BN < 32 || p.BN > 256 || p.num_stages < 2 || p.num_stages > 8 || (G != 1 && G != 2 && G != 3) ||
       (p.nbuf != 1 && p.nbuf != 2) || p.num_n_tiles * p.BN > kBiasFloats || p.units_per_stage < 1 ||
-      (p.n_groups * p.kb_per_tap) % p.units_per_stage != 0) {
+      p.m_batch < 1 || (p.m_batch > 1 && (p.BN != 32 || p.head || p.has_res || p.m_batch > 8)) ||
+      (p.m_batch > 1 && p.a_mode != 1) || (p.n_groups * p.kb_per_tap) % p.units_per_stage != 0) {
     set_error("conv_gemm: unsupported tile BN=%d G=%d stages=%d nbuf=%d n_tiles=%d", p.BN, G, p.num_stages, p.nbuf,
               p.num_n_tiles);
     return AY_EINVAL;
@@ -650,6 +699,7 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
     conv_gemm_kernel<GG, FF><<<grid, kThreads2, smem, stream>>>(tmA, tmB, tmOut, tmRes, tmResPF, p);                   \
   } while (0)
   if (G == 3) { if (is_fp16) AY_LAUNCH(3, true); else AY_LAUNCH(3, false); }
+  else if (G == 2) { if (is_fp16) AY_LAUNCH(2, true); else AY_LAUNCH(2, false); }
   else        { if (is_fp16) AY_LAUNCH(1, true); else AY_LAUNCH(1, false); }
 #undef AY_LAUNCH
   AY_CUDA(cudaGetLastError());

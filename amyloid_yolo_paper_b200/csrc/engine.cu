@@ -108,6 +108,7 @@ struct Layer {
   int cin = 0, cin_p = 0, cin_k = 0, cout_rows = 0, ktot = 0;   // cin_p: channels stored (x32); cin_k: K per tap (x64)
   int BN = 0, G = 1, a_rows = 128, stages = 0, nbuf = 1;
   int units_per_stage = 1;          // (group, k-block) units per pipeline stage
+  int m_batch = 1;                  // 256-row blocks per tile (first layer: 4)
   int b_resident = 0;               // weights stay in shared memory for the whole launch (single N tile, small K)
   int impl = 0;                     // 0 none, 1 tcgen05 gemm
   bool first = false;               // 3-channel first layer: GEMM over the staged 8-channel input x8
@@ -123,6 +124,8 @@ struct Layer {
   void* planes = nullptr;           // stride-2: parity planes [4][plane_rows][cin_p]
   long long plane_rows = 0;
   bool gather_fused = false;        // stride-2: the producer of the input writes the planes itself
+  bool s2_packed = false;           // stride-2 over 32 channels: column-parity pairs packed into 64-channel rows (see pass 3c)
+  void* w16_ref = nullptr;          // packed layers: weights in the plain tap-major layout for the CUDA-core reference
   int plane_consumer = -1;          // conv: index of the stride-2 conv whose planes this conv's epilogue fills
   int plane_mode = 0;               // conv: 1 = rows and planes, 2 = planes only (nothing else reads the rows)
   float* raw_f32 = nullptr;         // reference path scratch for heads
@@ -478,10 +481,15 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     int pc = -1;
     if (Ls[i - 1].d.type == AY_CONV && Ls[i - 1].impl == 1 && !Ls[i - 1].is_head) pc = i - 1;
     else if (Ls[i - 1].d.type == AY_SHORTCUT && Ls[i - 1].fused_into_prev) pc = i - 2;
-    if (pc >= 0 && Ls[pc].plane_consumer < 0 && in.pitch == in.Cp) {
+    if (pc >= 0 && Ls[pc].plane_consumer < 0) {      // (the planes have their own pitch: the input may live in a concat slice)
       Ls[pc].plane_consumer = i;
       Ls[pc].plane_mode = explicit_refs[i - 1].empty() ? 2 : 1;
       L.gather_fused = true;
+      // 32-channel input (64-byte pixels): the producer interleaves the two column-parity planes, so that a 128-byte
+      // row of a ROW-parity plane holds the pixel pair (x even | x odd).  Taps kw = 0,1 of a filter row are then one
+      // 64-channel k-block of box row r, and tap kw = 2 is the first half of box row r + 1: three 129-row A boxes per
+      // tile instead of nine half-empty ones, and 6 k-blocks of MMAs instead of 9.
+      if (in.Cp == 32 && !getenv("AY_NO_PACKED")) L.s2_packed = true;
     }
   }
 
@@ -510,19 +518,23 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       L.cin_p = in.Cp;
       L.cin_k = ay::round_up(L.cin_p, 64);
       L.ktot = taps * L.cin_k;
+      if (L.s2_packed) L.ktot = 6 * 64;       // per filter row: [kw0 | kw1] and [kw2 | zeros]
     }
     const int cout_p = ay::round_up(L.C, 32);
     if (L.is_head) L.BN = cout_p <= 256 ? cout_p : 256;
     else L.BN = (cout_p % 256 == 0) ? 256 : (cout_p % 128 == 0) ? 128 : (cout_p % 64 == 0) ? 64 : 32;
     L.cout_rows = ay::round_up(cout_p, L.BN);
-    L.G = (L.d.size == 3 && L.d.stride == 1 && !L.first) ? 3 : 1;
-    L.a_rows = L.first ? 18 : L.G == 3 ? 130 : 128;
+    L.G = L.s2_packed ? 2 : (L.d.size == 3 && L.d.stride == 1 && !L.first) ? 3 : 1;
+    // first layer: four 256-row blocks per tile (K is only 3 x 32: one barrier round and three loads per 1024 rows);
+    // each CTA's box is its 512 consecutive pixels + shift + taps = 66 rows of 8 pixels
+    if (L.first && !getenv("AY_NO_MBATCH")) L.m_batch = 4;
+    L.a_rows = L.first ? (128 * L.m_batch + 16) / 8 : L.G == 3 ? 130 : L.G == 2 ? 129 : 128;
     {
       // resident weights when this CTA's half of the matrix leaves room for the A ring;
       // units per stage: the largest divisor of the tile's unit count that keeps a stage <= 56 KB and >= 3 stages
       const int res_bytes = (L.BN / 2) * L.ktot * 2;
-      const int n_groups = L.first ? 3 : L.d.size == 1 ? 1 : L.d.stride == 1 ? 3 : 9;
-      const int units = n_groups * (L.cin_k / 64);
+      const int n_groups = L.first ? 3 : L.d.size == 1 ? 1 : (L.d.stride == 1 || L.s2_packed) ? 3 : 9;
+      const int units = n_groups * (L.s2_packed ? 1 : L.cin_k / 64);
       const bool try_res = L.cout_rows == L.BN && res_bytes <= 96 * 1024 && !getenv("AY_NO_RESIDENT");
       L.units_per_stage = 1;
       for (int pass = try_res ? 0 : 1; pass < 2 && L.stages == 0; ++pass) {
@@ -549,6 +561,7 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     }
     if (L.stages < 2) { set_error("layer %d: tile does not fit in shared memory", i); return AY_EINVAL; }
     AY_TRY(ay::dev_alloc(ctx, &L.w16, (size_t)L.cout_rows * L.ktot * 2, true));
+    if (L.s2_packed) AY_TRY(ay::dev_alloc(ctx, &L.w16_ref, (size_t)L.cout_rows * 9 * L.cin_k * 2, true));
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.cout_rows, true));
     AY_TRY(ay::make_map_2d(&L.tmB, L.w16, L.ktot, L.cout_rows, L.ktot, 64, L.BN / 2, ctx->is_fp16));
     // A boxes are always 64 channels wide; when the tensor stores only 32 (cin_p = 32) the upper half of the
@@ -558,7 +571,8 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       AY_TRY(ay::make_map_2d(&L.tmA, L.x8, 64, (ay::padded_rows(max_batch, ph0, pw0) + 7) / 8, 64, 64, L.a_rows,
                              ctx->is_fp16, /*swizzle=*/false));
     } else if (L.d.stride == 2) {
-      AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, 64, L.a_rows, ctx->is_fp16));
+      if (L.s2_packed) AY_TRY(ay::make_map_2d(&L.tmA, L.planes, 64, 2 * L.plane_rows, 64, 64, L.a_rows, ctx->is_fp16));
+      else AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, 64, L.a_rows, ctx->is_fp16));
     } else {
       AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, 64, L.a_rows, ctx->is_fp16));
     }
@@ -612,10 +626,25 @@ extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const flo
     AY_CUDA(cudaMemcpy(L.bias, b.data(), sizeof(float) * L.cout_rows, cudaMemcpyHostToDevice));
   } else {
     std::vector<uint16_t> r((size_t)L.cout_rows * L.ktot, 0);
-    for (int o = 0; o < cout; ++o)
-      for (int c = 0; c < cin; ++c)
-        for (int t = 0; t < taps; ++t)
-          r[(size_t)o * L.ktot + (size_t)t * L.cin_k + c] = ay::to16(w[((size_t)o * cin + c) * taps + t], ctx->is_fp16);
+    if (L.s2_packed) {
+      // k-block (kh, 0) = [kw0 | kw1], k-block (kh, 1) = [kw2 | zeros], 32 channels each half
+      const int kref = 9 * L.cin_k;
+      std::vector<uint16_t> rr((size_t)L.cout_rows * kref, 0);
+      for (int o = 0; o < cout; ++o)
+        for (int c = 0; c < cin; ++c)
+          for (int t = 0; t < 9; ++t) {
+            const int kh = t / 3, kw = t % 3;
+            const uint16_t v = ay::to16(w[((size_t)o * cin + c) * 9 + t], ctx->is_fp16);
+            r[(size_t)o * L.ktot + (size_t)(kh * 2 + (kw == 2)) * 64 + (kw == 1 ? 32 : 0) + c] = v;
+            rr[(size_t)o * kref + (size_t)t * L.cin_k + c] = v;
+          }
+      AY_CUDA(cudaMemcpy(L.w16_ref, rr.data(), rr.size() * 2, cudaMemcpyHostToDevice));
+    } else {
+      for (int o = 0; o < cout; ++o)
+        for (int c = 0; c < cin; ++c)
+          for (int t = 0; t < taps; ++t)
+            r[(size_t)o * L.ktot + (size_t)t * L.cin_k + c] = ay::to16(w[((size_t)o * cin + c) * taps + t], ctx->is_fp16);
+    }
     std::vector<float> b(L.cout_rows, 0.f);
     memcpy(b.data(), bias, sizeof(float) * cout);
     AY_CUDA(cudaMemcpy(L.w16, r.data(), r.size() * 2, cudaMemcpyHostToDevice));
@@ -699,7 +728,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   if (ctx->use_ref) {
     ay::RefConvParams r{};
     r.in = in.ptr; r.in_pitch = in.pitch; r.Cin_p = L.cin_p; r.Cin_k = L.cin_k; r.H = in.H; r.W = in.W;
-    r.w = L.w16; r.ktot = L.ktot; r.bias = L.bias; r.cout_p = L.is_head ? L.cout_rows : target->Cp;
+    r.w = L.s2_packed ? L.w16_ref : L.w16; r.ktot = L.s2_packed ? 9 * L.cin_k : L.ktot; r.bias = L.bias; r.cout_p = L.is_head ? L.cout_rows : target->Cp;
     r.size = L.d.size; r.stride = L.d.stride; r.leaky = L.d.leaky;
     r.residual = res ? res->ptr : nullptr; r.res_pitch = res ? res->pitch : 0;
     r.out = L.is_head ? nullptr : target->ptr; r.out_pitch = L.is_head ? 0 : target->pitch;
@@ -724,7 +753,8 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
 
   ay::ConvGemmParams q{};
   q.P = (int)ay::padded_rows(batch, L.H, L.W);
-  q.num_m_tiles = (q.P + 255) / 256;
+  q.m_batch = L.m_batch;
+  q.num_m_tiles = (q.P + 256 * L.m_batch - 1) / (256 * L.m_batch);
   q.num_n_tiles = L.cout_rows / L.BN;
   q.a_rows = L.a_rows;
   q.kb_per_tap = L.cin_k / 64;
@@ -745,6 +775,15 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
       q.a_row_off[kh] = (kh - 1) * Wq - 1;
       q.b_tap0[kh] = kh * 3;
     }
+  } else if (L.s2_packed) {
+    q.n_groups = 3;                       // one group per kh: box row r = taps kw 0,1; box row r + 1 = tap kw 2
+    q.kb_per_tap = 1;
+    for (int kh = 0; kh < 3; ++kh) {
+      const long long off = (long long)(kh & 1) * L.plane_rows + (kh >> 1) * Wq;
+      if (off > 0x7fffffffLL - (1LL << 26)) { set_error("layer %d: batch too large for 32-bit row offsets", i); return AY_EINVAL; }
+      q.a_row_off[kh] = (int)off;
+      q.b_tap0[kh] = kh * 2;
+    }
   } else {
     if (!L.gather_fused) {
       AY_TRY(ay::launch_s2_gather(in.ptr, in.pitch, L.cin_p / 8, batch, in.H, in.W, L.planes, L.plane_rows, st));
@@ -760,7 +799,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
       }
   }
   q.BN = L.BN; q.num_stages = L.stages; q.nbuf = L.nbuf; q.units_per_stage = L.units_per_stage;
-  q.num_acc = std::min(16, 512 / L.BN);
+  q.num_acc = std::min(16, 512 / (L.BN * L.m_batch));
   q.b_resident = L.b_resident;
   q.b_res_tiles = L.ktot / 64;
   q.a_mode = L.first ? 1 : 0;
@@ -789,6 +828,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
       q.plane_mode = L.plane_mode;
       q.planes = Cn.planes;
       q.plane_rows = Cn.plane_rows;
+      q.plane_packed = Cn.s2_packed ? 1 : 0;
       q.plane_pitch = target->Cp;
     }
   }
@@ -930,7 +970,7 @@ extern "C" int ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out
   else if (L.d.type == AY_SHORTCUT && L.fused_into_prev) producer = layer - 1;
   if (!ctx->use_ref && producer >= 0 && ctx->layers[producer].plane_mode == 2) {
     const Layer& Cn = ctx->layers[ctx->layers[producer].plane_consumer];
-    return ay::launch_dump_planes_nchw(Cn.planes, Cn.plane_rows, L.out.Cp, L.C, batch, L.H, L.W, ctx->is_fp16, out_nchw,
+    return ay::launch_dump_planes_nchw(Cn.planes, Cn.plane_rows, L.out.Cp, L.C, batch, L.H, L.W, ctx->is_fp16, Cn.s2_packed ? 1 : 0, out_nchw,
                                        static_cast<cudaStream_t>(stream));
   }
   return ay::launch_dump_nchw(L.out.ptr, L.out.pitch, L.C, batch, L.H, L.W, ctx->is_fp16, out_nchw,

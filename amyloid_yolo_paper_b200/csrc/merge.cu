@@ -43,6 +43,7 @@ struct TileScratch {
   Slot table[2][kTable];
   int gone[kPool];
   int snap[kPool];
+  unsigned char gflag[kPool];
 };
 
 __device__ __noinline__ long long hash_double(double v) {
@@ -91,13 +92,14 @@ constexpr int kSmallN = 48;                    // detections per tile handled ou
 constexpr int kSmallPool = 2 * kSmallN;
 constexpr int kSmallSlots = 512;               // the set never holds more than n <= 48 live keys: resize() asks for the
                                                // power of two above 4 * used <= 192, i.e. at most 256 slots
-constexpr size_t kSmallBytes = sizeof(Entry) * kSmallPool + 2 * sizeof(Slot) * kSmallSlots + 2 * sizeof(int) * kSmallPool;
+constexpr size_t kSmallBytes = sizeof(Entry) * kSmallPool + 2 * sizeof(Slot) * kSmallSlots + 2 * sizeof(int) * kSmallPool + kSmallPool;
 
 struct Work {            // where this tile's working set lives
   Entry* pool;
   Slot* table[2];
   int* gone;
   int* snap;
+  unsigned char* gflag;   // gflag[i] != 0: the VALUE of pool[i] is in the reference's `gone` list
   int pool_cap;
 };
 
@@ -221,11 +223,12 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
     work.table[1] = work.table[0] + kSmallSlots;
     work.gone = reinterpret_cast<int*>(work.table[1] + kSmallSlots);
     work.snap = work.gone + kSmallPool;
+    work.gflag = reinterpret_cast<unsigned char*>(work.snap + kSmallPool);
     work.pool_cap = kSmallPool;
   } else {
     TileScratch* g = scratch + b;
     work.pool = g->pool; work.table[0] = g->table[0]; work.table[1] = g->table[1];
-    work.gone = g->gone; work.snap = g->snap; work.pool_cap = kPool;
+    work.gone = g->gone; work.snap = g->snap; work.gflag = g->gflag; work.pool_cap = kPool;
   }
   Work* ts = &work;
   PySet live;
@@ -241,6 +244,7 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
     e.v[5] = (double)in[r * 7 + 5];
     e.v[6] = (double)in[r * 7 + 6];
     e.hash = hash_tuple7(e.v);
+    ts->gflag[npool] = 0;
     live.add(npool);
     ++npool;   // duplicates stay in the pool but not in the set
   }
@@ -253,16 +257,18 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
       for (int s = 0; s <= live.mask; ++s)
         if (tab[s].idx >= 0) ts->snap[ns++] = tab[s].idx;
     }
+    // The reference skips a pair when either tuple equals (by value) a member of `gone`, a list that persists across
+    // passes.  Live keys are value-unique, so a snapshot entry can only equal a gone one if it IS that entry or was
+    // created later with the same value: one flag per pool entry, set on removal and checked against the list once at
+    // creation, replaces the O(n) list scan per pair.
     for (int i = 0; i < ns; ++i) {
       for (int j = i + 1; j < ns; ++j) {
+        if (ts->gflag[ts->snap[i]]) break;
+        if (ts->gflag[ts->snap[j]]) continue;
         const Entry& A = ts->pool[ts->snap[i]];
         const Entry& B = ts->pool[ts->snap[j]];
         const double la = A.v[6], lb = B.v[6];
         if (!((la == 1.0 && lb == 1.0) || (la == 0.0 && lb == 0.0))) continue;
-        bool skip = false;
-        for (int g = 0; g < ngone && !skip; ++g)
-          skip = same_tuple(ts->pool[ts->gone[g]], A) || same_tuple(ts->pool[ts->gone[g]], B);
-        if (skip) continue;
         const long long x1 = trunc_ll(A.v[0]), y1 = trunc_ll(A.v[1]);
         const long long w1 = trunc_ll(A.v[2] - A.v[0]), h1 = trunc_ll(A.v[3] - A.v[1]);
         const long long x2 = trunc_ll(B.v[0]), y2 = trunc_ll(B.v[1]);
@@ -280,12 +286,19 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
         N.v[6] = la;
         N.hash = hash_tuple7(N.v);
         if (live.find(N) >= 0) continue;
+        {
+          unsigned char f = 0;
+          for (int g = 0; g < ngone && !f; ++g) f = same_tuple(ts->pool[ts->gone[g]], N) ? 1 : 0;
+          ts->gflag[npool] = f;
+        }
         live.add(npool);
         ++npool;
         live.remove_slot(live.find(A));
         live.remove_slot(live.find(B));
         ts->gone[ngone++] = ts->snap[i];
         ts->gone[ngone++] = ts->snap[j];
+        ts->gflag[ts->snap[i]] = 1;
+        ts->gflag[ts->snap[j]] = 1;
         changed = true;
       }
     }

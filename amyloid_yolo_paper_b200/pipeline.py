@@ -110,15 +110,56 @@ class TileDetector:
         original-tile pixels) or ``None`` where nothing was detected — the per-image value
         ``detect.py:127-133`` ends up with."""
         out = []
+        if not tiles.is_cuda:
+            return self._detect_host(tiles, original_shape)
         for lo in range(0, tiles.shape[0], self.max_batch):
             chunk = tiles[lo:lo + self.max_batch]
-            if not chunk.is_cuda:
-                chunk = chunk.to(self.device, non_blocking=True)
             rows, counts = self.run_device(chunk.contiguous(), original_shape)
-            counts_h = counts.cpu()                 # synchronises the stream
-            self.check()
-            kmax = int(counts_h.max()) if counts_h.numel() else 0
-            rows_h = rows[:, :max(kmax, 1)].cpu()
-            for b, k in enumerate(counts_h.tolist()):
-                out.append(rows_h[b, :k].clone() if k > 0 else None)
+            self._collect(rows, counts, out)
+        return out
+
+    def _collect(self, rows, counts, out):
+        counts_h = counts.cpu()                 # synchronises the compute stream
+        self.check()
+        kmax = int(counts_h.max()) if counts_h.numel() else 0
+        rows_h = rows[:, :max(kmax, 1)].cpu()
+        for b, k in enumerate(counts_h.tolist()):
+            out.append(rows_h[b, :k].clone() if k > 0 else None)
+
+    def _detect_host(self, tiles, original_shape):
+        """Host input: sub-batches are uploaded on a copy stream into two device buffers while the previous
+        sub-batch computes, so the H2D time of a large batch hides behind the convolutions."""
+        n = tiles.shape[0]
+        sub = self.max_batch if self.max_batch < 128 else max(32, self.max_batch // 4)
+        main = torch.cuda.current_stream(self.device)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._stage = [None, None]
+        shape = (sub,) + tuple(tiles.shape[1:])
+        for i in range(2):
+            if self._stage[i] is None or self._stage[i].shape != shape or self._stage[i].dtype != tiles.dtype:
+                self._stage[i] = torch.empty(shape, dtype=tiles.dtype, device=self.device)
+        spans = [(lo, min(n, lo + sub)) for lo in range(0, n, sub)]
+        copied = [torch.cuda.Event() for _ in spans]
+        freed = [None, None]
+
+        def upload(i):
+            lo, hi = spans[i]
+            with torch.cuda.stream(self._copy_stream):
+                if freed[i % 2] is not None:
+                    self._copy_stream.wait_event(freed[i % 2])      # the compute that read this buffer has finished
+                self._stage[i % 2][:hi - lo].copy_(tiles[lo:hi], non_blocking=True)
+                copied[i].record(self._copy_stream)
+
+        out = []
+        upload(0)
+        for i, (lo, hi) in enumerate(spans):
+            if i + 1 < len(spans):
+                upload(i + 1)
+            main.wait_event(copied[i])
+            rows, counts = self.run_device(self._stage[i % 2][:hi - lo], original_shape)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            freed[i % 2] = ev
+            self._collect(rows, counts, out)
         return out
