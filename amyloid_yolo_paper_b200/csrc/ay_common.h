@@ -74,6 +74,7 @@ struct ConvGemmParams {
   void* planes;
   long long plane_rows;
   int plane_pitch;
+  int up_mode;           // the only consumer is a x2 nearest upsample: write the 2x2 block into ITS buffer (out_ptr/out_pitch)
   int plane_packed;      // 32-channel producer: the column-parity pair shares one 64-channel row of a ROW-parity plane
   // fused YOLO decode (head convolutions)
   int head;

@@ -498,13 +498,21 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // and a proxy fence per chunk and made the epilogue, not the tensor pipe, the bound of the 3x3 layers.)
         // Chunk c of a tile is 32 accumulator columns: channels c*32.. of the tile's rows, or - for row-batched tiles
         // (m_batch > 1, BN = 32) - all 32 channels of the rows of sub-block c.
-        struct RowTarget { bool store, zero; uint16_t* out; uint16_t* plane; };
+        struct RowTarget { bool store, zero, up; uint16_t* out; uint16_t* plane; };
         auto row_target = [&](int mr, int image, int py, int px, bool is_halo) {
           RowTarget t;
           t.store = mr < p.P;
           t.zero = is_halo | !t.store;
           t.out = static_cast<uint16_t*>(p.out_ptr) + (size_t)mr * p.out_pitch + n0;
           t.plane = nullptr;
+          t.up = false;
+          if (p.up_mode) {
+            // nearest x2 upsample fused (models.py:86-96): interior pixel (py, px) fills the 2x2 block whose top-left
+            // padded coordinate is (2py-1, 2px-1) of the consumer's [2H+2, 2W+2] grid; halo rows write nothing
+            const int Wt = 2 * (p.Wp - 2) + 2, Ht = 2 * (p.Hp - 2) + 2;
+            t.up = t.store && !is_halo;
+            t.out = static_cast<uint16_t*>(p.out_ptr) + (((size_t)image * Ht + (2 * py - 1)) * Wt + (2 * px - 1)) * p.out_pitch + n0;
+          }
           if (p.plane_mode != 0) {
             // padded output pixel (py, px) -> plane (py&1, px&1), position (py/2 + 1, px/2 + 1) of the half-size padded grid
             const int Hq2 = (p.Hp - 2) / 2 + 2, Wq2 = (p.Wp - 2) / 2 + 2;
@@ -587,7 +595,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               }
               o[e] = t.zero ? 0u : pack_pair<FP16>(lo, hi);
             }
-            if (t.store && !(p.dbg & 4)) {
+            if (p.up_mode) {
+              if (t.up && !(p.dbg & 4)) {
+                const size_t down = (size_t)(2 * (p.Wp - 2) + 2) * p.out_pitch;      // one row of the upsampled grid
+#pragma unroll
+                for (int d = 0; d < 4; ++d) {
+                  uint16_t* dst = t.out + (d >> 1) * down + (d & 1) * p.out_pitch + ch;
+                  stg256(dst, &o[0]);
+                  stg256(dst + 16, &o[8]);
+                }
+              }
+            } else if (t.store && !(p.dbg & 4)) {
               if (p.plane_mode != 2) {
                 stg256(t.out + ch, &o[0]);
                 stg256(t.out + ch + 16, &o[8]);

@@ -127,6 +127,8 @@ struct Layer {
   bool s2_packed = false;           // stride-2 over 32 channels: column-parity pairs packed into 64-channel rows (see pass 3c)
   void* w16_ref = nullptr;          // packed layers: weights in the plain tap-major layout for the CUDA-core reference
   int plane_consumer = -1;          // conv: index of the stride-2 conv whose planes this conv's epilogue fills
+  int up_consumer = -1;             // conv: index of the [upsample] block whose output this conv's epilogue writes directly
+  bool fused_into_producer = false; // upsample: written by the producing conv
   int plane_mode = 0;               // conv: 1 = rows and planes, 2 = planes only (nothing else reads the rows)
   float* raw_f32 = nullptr;         // reference path scratch for heads
   // tmA: a_rows x 64-channel box of the input (or parity planes); tmB: BN/2 x 64 box of the weights;
@@ -493,6 +495,16 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     }
   }
 
+  // ---- pass 3d: conv -> [upsample] with no other reader of the conv: the epilogue writes the 2x2 blocks itself
+  for (int i = 0; i + 1 < n_layers; ++i) {
+    Layer& L = Ls[i];
+    if (L.d.type != AY_CONV || L.impl != 1 || L.is_head || L.fused_shortcut >= 0 || L.plane_consumer >= 0) continue;
+    if (Ls[i + 1].d.type != AY_UPSAMPLE || !explicit_refs[i].empty() || getenv("AY_NO_UPFUSE")) continue;
+    if (i + 2 < n_layers && Ls[i + 2].d.type != AY_ROUTE) continue;      // (the conv's own rows would be needed otherwise)
+    L.up_consumer = i + 1;
+    Ls[i + 1].fused_into_producer = true;
+  }
+
   const int ph0 = img_size, pw0 = img_size;
   // ---- pass 4: convolution resources
   for (int i = 0; i < n_layers; ++i) {
@@ -822,6 +834,11 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
     q.has_res = res ? 1 : 0;
     q.cout = L.C;
     q.out_ptr = target->ptr; q.out_pitch = target->pitch;
+    if (L.up_consumer >= 0) {
+      const ActView& up = Ls[L.up_consumer].out;
+      q.up_mode = 1;
+      q.out_ptr = up.ptr; q.out_pitch = up.pitch;
+    }
     q.res_ptr = res ? res->ptr : nullptr; q.res_pitch = res ? res->pitch : 0;
     if (L.plane_consumer >= 0) {
       const Layer& Cn = Ls[L.plane_consumer];
@@ -885,6 +902,7 @@ extern "C" int ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch
         break;
       }
       case AY_UPSAMPLE: {
+        if (L.fused_into_producer && !ctx->use_ref) break;
         const ActView& in = Ls[i - 1].out;
         AY_TRY(ay::launch_upsample2(in.ptr, in.pitch, in.Cp, batch, in.H, in.W, L.out.ptr, L.out.pitch, st));
         ++ctx->launches;
@@ -963,7 +981,10 @@ extern "C" int ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out
     return AY_EINVAL;
   }
   const Layer& L = ctx->layers[layer];
-  if (!L.out.ptr) { set_error("layer %d is fused into its consumer and has no stored output", layer); return AY_EINVAL; }
+  if (!L.out.ptr || (!ctx->use_ref && L.up_consumer >= 0)) {
+    set_error("layer %d is fused into its consumer and has no stored output", layer);
+    return AY_EINVAL;
+  }
   // a tensor read only by a stride-2 convolution is stored as that convolution's parity planes
   int producer = -1;
   if (L.d.type == AY_CONV && L.fused_shortcut < 0) producer = layer;

@@ -57,6 +57,15 @@ def main():
             if r:
                 best = [min(a, b) for a, b in zip(best, ms)]
         cols[dbg] = best
+    # whole forward without the per-layer events (launch gaps included), 10 back-to-back calls
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        _lib.check(eng.lib.ay_forward(eng.ctx, ctypes.c_void_p(tiles.data_ptr()), _lib.AY_IN_U8_HWC, B, args.tile, args.tile,
+                                      ctypes.c_void_p(out.data_ptr()), st))
+    e1.record()
+    torch.cuda.synchronize()
+    whole_ms = e0.elapsed_time(e1) / 10
     cnt = (ctypes.c_ulonglong * (16 * n))()
     _lib.check(eng.lib.ay_debug_counters(eng.ctx, cnt, n))
     _lib.check(eng.lib.ay_debug_set(eng.ctx, 0))
@@ -106,6 +115,7 @@ def main():
     hdr = "idx layer                        " + " ".join("dbg=%-4d" % k for k in settings)
     text = "\n".join([hdr] + lines + ["sum us                           " + " ".join("%8.0f" % tot[k] for k in settings) +
                                       "   bound %7.0f" % tot_bound,
+                                      "whole forward, 10 calls back to back: %.0f us per call" % (whole_ms * 1e3),
                                       "batch %d, peaks %s" % (B, peaks)])
     print(text)
     if args.out:
