@@ -234,6 +234,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int R = p.m_batch;
   const int tile_rows = 2 * kRowsPerCta * R;
   const int acc_cols = p.BN * R;
+  // tiles of <= 4 chunks (32 accumulator columns each): the two epilogue warps of a TMEM lane quarter take alternate tiles
+  const bool tile_split = (acc_cols >> 5) == 1 || ((acc_cols >> 5) <= kMaxChunksPerWarp && !p.head);
   const uint32_t unit_bytes = a_region + (p.b_resident ? 0u : G * b_tile);
   const uint32_t stage_bytes = (uint32_t)U * unit_bytes;
   const uint32_t tx_bytes = (uint32_t)U * ((uint32_t)p.a_rows * kRowBytes + (p.b_resident ? 0u : G * b_tile));   // one CTA's loads per stage
@@ -280,7 +282,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int a = 0; a < kMaxAcc; ++a) {
       bar_init(tfull_bar(a), 1);                // tcgen05.commit multicast
       // leader's copy: the epilogue warps of both CTAs that work on a tile (all 8, or 4 when BN = 32: see `split`)
-      bar_init(tempty_bar(a), acc_cols == 32 ? kEpiWarps : 2 * kEpiWarps);
+      bar_init(tempty_bar(a), tile_split ? kEpiWarps : 2 * kEpiWarps);
     }
     for (int w = 0; w < kEpiWarps; ++w)
       for (int b = 0; b < kMaxStageBufs; ++b) bar_init(res_bar(w, b), 1);   // residual TMA loads, per epilogue warp
@@ -469,22 +471,39 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // A tile with a single 32-column chunk would leave half of the epilogue warps idle and make the per-tile
     // latency chain (wait, tcgen05.ld, math, store, arrive) the bound; there the two warps of a quarter take
     // alternate TILES instead of alternate chunks (tile parity = accumulator buffer = `half`).
-    const bool split = nchunks == 1;
+    // The epilogue of one warp is a long dependent instruction stream (~550 instructions per tile and chunk at IPC ~0.2),
+    // so tiles of up to four chunks are not shared between the two warps of a quarter: they take alternate TILES and
+    // all chunks of their quarter, which keeps two tiles in flight per quarter and halves the per-tile fixed work.
+    const bool split = tile_split;
     const int c_first = split ? 0 : half;
-    int it = 0;
-    for (int tile = first_tile; tile < total_tiles; tile += n_clusters, ++it) {
-      if (split && (it & 1) != half) continue;
-      const int acc = it % num_acc;
-      const uint32_t acc_phase = (uint32_t)(it / num_acc) & 1u;
-      const long long e0 = prof ? clock64() : 0;
-      const int m0 = (tile / p.num_n_tiles) * tile_rows + (int)rank * kRowsPerCta * R;
-      const int n0 = (tile % p.num_n_tiles) * p.BN;
-      const int m = m0 + row_in_tile;
+    const int c_step = split ? 1 : 2;
+    // Tile sequence of this warp and the row it owns in each tile, kept incrementally (tile -> (m tile, n tile) ->
+    // (image, y, x) costs four integer divisions, ~100 dependent instructions, if recomputed per tile).
+    const int t_step = n_clusters * (split ? 2 : 1);
+    const int it_step = split ? 2 : 1;
+    const int nnt = p.num_n_tiles;
+    int tile = first_tile + (split ? half * n_clusters : 0);
+    int acc = (split ? half : 0) % num_acc;
+    uint32_t acc_phase = 0;
+    int ntile = tile % nnt;
+    int m = (tile / nnt) * tile_rows + (int)rank * kRowsPerCta * R + row_in_tile;
+    int img = m / hw;
+    int yy = (m - img * hw) / p.Wp;
+    int xx = m - img * hw - yy * p.Wp;
+    const int dq = t_step / nnt, dr = t_step - dq * nnt;       // tile += t_step  ==  (m tile, n tile) += (dq, dr) with carry
+    const int qrows = dq * tile_rows;
+    const int qI = qrows / hw, qY = (qrows - qI * hw) / p.Wp, qX = qrows - qI * hw - qY * p.Wp;
+    const int tI = tile_rows / hw, tY = (tile_rows - tI * hw) / p.Wp, tX = tile_rows - tI * hw - tY * p.Wp;
+    auto advance_row = [&](int dI, int dY, int dX) {
+      xx += dX;
+      if (xx >= p.Wp) { xx -= p.Wp; ++yy; }
+      yy += dY;
+      if (yy >= p.Hp) { yy -= p.Hp; ++img; }
+      img += dI;
+    };
+    for (; tile < total_tiles; tile += t_step) {
+      const int n0 = ntile * p.BN;
       const bool in_range = m < p.P;
-      const int img = m / hw;
-      const int pix = m - img * hw;
-      const int yy = pix / p.Wp;
-      const int xx = pix - yy * p.Wp;
       const bool halo = (yy == 0) | (yy == p.Hp - 1) | (xx == 0) | (xx == p.Wp - 1);
 
       if (p.dbg & 64) {                                          // ablation: no epilogue work at all
@@ -530,12 +549,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         };
         const RowTarget t0 = row_target(m, img, yy, xx, halo);
         if (has_res) {
-          // pull the residual rows of the tile two rounds ahead into L2
-          const int nt = tile + 2 * n_clusters;
-          const long long mp = (long long)(nt / p.num_n_tiles) * tile_rows + (int)rank * kRowsPerCta * R + row_in_tile;
-          if (nt < total_tiles && mp < p.P) {
-            const uint16_t* pf = static_cast<const uint16_t*>(p.res_ptr) + (size_t)mp * p.res_pitch + (nt % p.num_n_tiles) * p.BN;
-            for (int l = half; l < (p.BN >> 6); l += 2)
+          // pull this thread's residual row of its tile two steps ahead into L2 (single-N-tile layers: the small tiles
+          // whose MMAs are too short to hide an HBM round trip)
+          const long long mp = (long long)m + 2LL * qrows;
+          if (nnt == 1 && mp < p.P) {
+            const uint16_t* pf = static_cast<const uint16_t*>(p.res_ptr) + (size_t)mp * p.res_pitch;
+            for (int l = split ? 0 : half; l < (p.BN >> 6); l += c_step)
               asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + l * 64) : "memory");
           }
         }
@@ -544,7 +563,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint16_t* res_row = static_cast<const uint16_t*>(p.res_ptr) + (size_t)m * p.res_pitch + n0;
 #pragma unroll
           for (int i = 0; i < kMaxChunksPerWarp; ++i) {
-            const int c = c_first + 2 * i;
+            const int c = c_first + c_step * i;
             if (c < nchunks) {
               ldg256(res_row + c * 32, &res[i][0]);
               ldg256(res_row + c * 32 + 16, &res[i][8]);
@@ -556,7 +575,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t t_acc = tmem_base + (uint32_t)(acc * acc_cols) + lane_addr;
 #pragma unroll
         for (int i = 0; i < kMaxChunksPerWarp; ++i) {
-          const int c = c_first + 2 * i;
+          const int c = c_first + c_step * i;
           if (c < nchunks) {
             uint32_t v[32];
             tmem_load32(t_acc + (uint32_t)(c * 32), v);
@@ -627,7 +646,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols +
                        ((size_t)gy * Gd + gx) * p.dec_cols;
         const size_t a_step = (size_t)Gd * Gd * p.dec_cols;
-        for (int c = c_first; c < nchunks; c += 2) {
+        for (int c = c_first; c < nchunks; c += c_step) {
           uint32_t v[32];
           tmem_load32(t_acc + (uint32_t)(c * 32), v);
           const int ch0 = n0 + c * 32;
@@ -649,13 +668,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
-      if (prof && ew == 0 && lane == 0) { pc[1] += clock64() - e0; pc[2] += 1; }
       // this warp is done reading the accumulator: one arrival per warp on the LEADER's barrier
       fence_before();
       __syncwarp();
-      if (lane == 0) bar_arrive_remote(map_to_cta(tempty_bar(acc), 0));
+      if (lane == 0) bar_arrive_remote(tempty_bar(acc) & kLeaderMask);
+      // next tile of this warp
+      acc += it_step;
+      if (acc >= num_acc) { acc -= num_acc; acc_phase ^= 1u; }
+      ntile += dr;
+      m += qrows;
+      advance_row(qI, qY, qX);
+      if (ntile >= nnt) {
+        ntile -= nnt;
+        m += tile_rows;
+        advance_row(tI, tY, tX);
+      }
     }
-    if (prof && ew == 0 && lane == 0) { atomicAdd(p.prof + 8, (unsigned long long)pc[1]); atomicAdd(p.prof + 9, (unsigned long long)pc[2]); }
   }
 
   // both CTAs must stay resident until the pair's last MMA, commit and remote arrive have landed
