@@ -57,15 +57,17 @@ class TileDetector:
         self.nms_rows = torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev)
         self.nms_keep = torch.empty((B, self.cap), dtype=torch.int32, device=dev)
         self.nms_counts = torch.empty((B,), dtype=torch.int32, device=dev)
-        self.out_rows = torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev)
-        self.out_counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        # two result slots: the host path reads slot i while the device fills slot i+1
+        self._out_rows = [torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev) for _ in range(2)]
+        self._out_counts = [torch.empty((B,), dtype=torch.int32, device=dev) for _ in range(2)]
+        self.out_rows, self.out_counts = self._out_rows[0], self._out_counts[0]
         self.launches_per_batch = 0
 
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     # ------------------------------------------------------------------ device side
-    def run_device(self, tiles, original_shape=None):
+    def run_device(self, tiles, original_shape=None, slot=0):
         """tiles: CUDA uint8 [B,H,H,3] (B <= max_batch) or CUDA fp32 [B,3,S,S].
         Enqueues the whole chain on the current stream; returns views
         ``(rows [B,cap,7], counts [B])`` of internal buffers (valid until the next call)."""
@@ -93,11 +95,11 @@ class TileDetector:
                                   self.cap, st))
             _lib.check(lib.ay_rescale_merge(ctx, _ptr(self.nms_rows), _ptr(self.nms_counts), B, self.cap,
                                             self.img_size, int(original_shape[0]), int(original_shape[1]),
-                                            1 if self.merge_boxes else 0, _ptr(self.out_rows),
-                                            _ptr(self.out_counts), st))
+                                            1 if self.merge_boxes else 0, _ptr(self._out_rows[slot]),
+                                            _ptr(self._out_counts[slot]), st))
         # forward kernels + 4 NMS kernels + 1 rescale/merge kernel
         self.launches_per_batch = self.engine.launch_count() + 4 + 1
-        return self.out_rows[:B], self.out_counts[:B]
+        return self._out_rows[slot][:B], self._out_counts[slot][:B]
 
     def check(self):
         with torch.cuda.device(self.device):
@@ -123,43 +125,84 @@ class TileDetector:
         self.check()
         kmax = int(counts_h.max()) if counts_h.numel() else 0
         rows_h = rows[:, :max(kmax, 1)].cpu()
+        self.d2h_bytes = getattr(self, "d2h_bytes", 0) + counts_h.numel() * 4 + rows_h.numel() * 4
         for b, k in enumerate(counts_h.tolist()):
             out.append(rows_h[b, :k].clone() if k > 0 else None)
 
     def _detect_host(self, tiles, original_shape):
-        """Host input: sub-batches are uploaded on a copy stream into two device buffers while the previous
-        sub-batch computes, so the H2D time of a large batch hides behind the convolutions."""
+        """Host input.  Sub-batches are uploaded on a copy stream into two device buffers while the previous one
+        computes (a small first sub-batch keeps the exposed part of the H2D short); results come back on a third
+        stream from two result slots, so the compute stream never waits for the host between sub-batches."""
         n = tiles.shape[0]
-        sub = self.max_batch if self.max_batch < 128 else max(32, self.max_batch // 4)
         main = torch.cuda.current_stream(self.device)
         if getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._d2h_stream = torch.cuda.Stream(device=self.device)
             self._stage = [None, None]
-        shape = (sub,) + tuple(tiles.shape[1:])
+            self._counts_h = [torch.empty((self.max_batch,), dtype=torch.int32).pin_memory() for _ in range(2)]
+            self._rows_h = [torch.empty((self.max_batch, self.cap, 7), dtype=torch.float32).pin_memory() for _ in range(2)]
+        big = self.max_batch if self.max_batch < 128 else self.max_batch // 2
+        spans, lo = [], 0
+        while lo < n:
+            left = n - lo
+            if self.max_batch >= 128 and lo % self.max_batch == 0 and left > big // 2:
+                size = big // 4                      # first sub-batch of a batch: short, its upload is exposed
+            elif self.max_batch >= 128 and lo % self.max_batch == big // 4:
+                size = big - big // 4
+            else:
+                size = big
+            spans.append((lo, min(n, lo + size)))
+            lo = spans[-1][1]
+        shape = (big,) + tuple(tiles.shape[1:])
         for i in range(2):
             if self._stage[i] is None or self._stage[i].shape != shape or self._stage[i].dtype != tiles.dtype:
                 self._stage[i] = torch.empty(shape, dtype=tiles.dtype, device=self.device)
-        spans = [(lo, min(n, lo + sub)) for lo in range(0, n, sub)]
         copied = [torch.cuda.Event() for _ in spans]
-        freed = [None, None]
+        computed = [torch.cuda.Event() for _ in spans]
+        fetched = [None] * len(spans)
 
         def upload(i):
             lo, hi = spans[i]
             with torch.cuda.stream(self._copy_stream):
-                if freed[i % 2] is not None:
-                    self._copy_stream.wait_event(freed[i % 2])      # the compute that read this buffer has finished
+                if i >= 2:
+                    self._copy_stream.wait_event(computed[i - 2])    # the compute that read this buffer has finished
                 self._stage[i % 2][:hi - lo].copy_(tiles[lo:hi], non_blocking=True)
                 copied[i].record(self._copy_stream)
 
+        def fetch(i):            # D2H of slot i % 2 on its own stream, after the compute of sub-batch i
+            lo, hi = spans[i]
+            with torch.cuda.stream(self._d2h_stream):
+                self._d2h_stream.wait_event(computed[i])
+                self._counts_h[i % 2][:hi - lo].copy_(self._out_counts[i % 2][:hi - lo], non_blocking=True)
+                self._rows_h[i % 2][:hi - lo].copy_(self._out_rows[i % 2][:hi - lo], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._d2h_stream)
+                fetched[i] = ev
+
+        def collect(i, out):
+            lo, hi = spans[i]
+            fetched[i].synchronize()
+            counts = self._counts_h[i % 2][:hi - lo].tolist()
+            if min(counts) < 0:
+                self.check()                         # raises the capacity error with its message
+            rows_h = self._rows_h[i % 2]
+            for b, k in enumerate(counts):
+                out.append(rows_h[b, :k].clone() if k > 0 else None)
+
         out = []
+        self.d2h_bytes = sum((hi - lo) * (4 + self.cap * 28) for lo, hi in spans)    # counts + padded rows copied back
         upload(0)
         for i, (lo, hi) in enumerate(spans):
             if i + 1 < len(spans):
                 upload(i + 1)
             main.wait_event(copied[i])
-            rows, counts = self.run_device(self._stage[i % 2][:hi - lo], original_shape)
-            ev = torch.cuda.Event()
-            ev.record(main)
-            freed[i % 2] = ev
-            self._collect(rows, counts, out)
+            if i >= 2:
+                main.wait_event(fetched[i - 2])      # result slot i % 2 has been read back
+            self.run_device(self._stage[i % 2][:hi - lo], original_shape, slot=i % 2)
+            computed[i].record(main)
+            fetch(i)
+            if i >= 1:
+                collect(i - 1, out)
+        collect(len(spans) - 1, out)
+        self.check()
         return out
