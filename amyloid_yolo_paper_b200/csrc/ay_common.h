@@ -78,6 +78,7 @@ struct ConvGemmParams {
   int plane_packed;      // 32-channel producer: the column-parity pair shares one 64-channel row of a ROW-parity plane
   // fused YOLO decode (head convolutions)
   int head;
+  int head_stage_bytes;  // per epilogue warp: n_anchors * 32 * dec_cols floats when the head fits one 32-column chunk, else 0
   float* dec_out;        // [B, dec_rows_total, dec_cols]
   int dec_rows_total, dec_row_off, dec_cols, n_anchors, cout;
   float stride;
@@ -89,7 +90,8 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
                      const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
                      cudaStream_t stream);
 int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident);
-void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int* stages, int* nbuf);
+void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int extra_bytes, int* stages, int* nbuf);
+constexpr int kConvEpilogueWarps = 8;
 
 // aux_kernels.cu ------------------------------------------------------------
 struct FirstConvParams {

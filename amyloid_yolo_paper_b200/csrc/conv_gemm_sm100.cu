@@ -241,7 +241,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t tx_bytes = (uint32_t)U * ((uint32_t)p.a_rows * kRowBytes + (p.b_resident ? 0u : G * b_tile));   // one CTA's loads per stage
   const int S = p.num_stages;
   const uint32_t staging_base = ring_base + S * stage_bytes;
-  const uint32_t bar_base = staging_base;           // (the epilogue stages nothing in shared memory any more)
+  // head convolutions with a single chunk stage their decoded rows here (one buffer per epilogue warp)
+  const uint32_t bar_base = staging_base + (uint32_t)kEpiWarps * (uint32_t)p.head_stage_bytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * S + a); };
@@ -646,26 +647,60 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols +
                        ((size_t)gy * Gd + gx) * p.dec_cols;
         const size_t a_step = (size_t)Gd * Gd * p.dec_cols;
+        // Decoded rows of consecutive pixels are consecutive in memory (dec_cols floats each, halo pixels skipped), so the
+        // valid rows of this warp form ONE contiguous span per anchor: staged in shared memory and written with full
+        // 128-byte store instructions instead of dec_cols scalar stores per row at a 28-byte stride.
+        const bool valid = in_range && !halo;
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+        const int rank_v = __popc(vmask & ((1u << lane) - 1u));
+        const int nvalid = __popc(vmask);
+        const int lane0 = vmask ? __ffs(vmask) - 1 : 0;
+        const int img_first = __shfl_sync(0xffffffffu, img, lane0);     // (every lane takes part: no short-circuit around it)
+        const bool one_image = __all_sync(0xffffffffu, !valid || img == img_first) != 0;
+        const bool staged = p.head_stage_bytes > 0 && one_image;
+        float* hs = reinterpret_cast<float*>(smem_raw + (staging_base - smem_addr(smem_raw)) + (uint32_t)ew * (uint32_t)p.head_stage_bytes);
         for (int c = c_first; c < nchunks; c += c_step) {
           uint32_t v[32];
           tmem_load32(t_acc + (uint32_t)(c * 32), v);
           const int ch0 = n0 + c * 32;
+          // branch-free per channel, so that the 32 independent exp / reciprocal chains overlap (with an if-chain on the
+          // field index every channel waited for the previous one's MUFU latencies)
+          float r[32];
+          int aj = ch0 / p.dec_cols, fj = ch0 - aj * p.dec_cols;  // running (anchor, field) of channel ch0 + j
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (ch0 + j >= p.cout) break;                         // (warp-uniform: channels past cout do not exist)
+            const int ch = ch0 + j;
+            const bool wh = (fj == 2) | (fj == 3);
+            const float t = __uint_as_float(v[j]) + s_bias[ch];
+            const float e = (p.dbg & 512) ? t : expf(wh ? t : -t);          // (ablation 512: no transcendental)
+            const float sg = 1.0f / (1.0f + e);                                   // sigmoid(t), as sigmoid_acc
+            const float anchor = (fj == 2) ? p.anchor_w[aj] : p.anchor_h[aj];
+            const float off = (fj == 0) ? (float)gx : (float)gy;
+            const float box = wh ? __fmul_rn(__fmul_rn(e, anchor), p.stride) : __fmul_rn(__fadd_rn(sg, off), p.stride);
+            r[j] = (fj < 4) ? box : sg;
+            if (++fj == p.dec_cols) { fj = 0; aj = min(aj + 1, p.n_anchors - 1); }
+          }
           int a = ch0 / p.dec_cols, fi = ch0 - a * p.dec_cols;   // running (anchor, field) of channel ch
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int ch = ch0 + j;
-            if (ch < p.cout && in_range && !halo) {
-              const float t = __uint_as_float(v[j]) + s_bias[ch];
-              float r;
-              if (fi == 0) r = __fmul_rn(__fadd_rn(sigmoid_acc(t), (float)gx), p.stride);
-              else if (fi == 1) r = __fmul_rn(__fadd_rn(sigmoid_acc(t), (float)gy), p.stride);
-              else if (fi == 2) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_w[a]), p.stride);
-              else if (fi == 3) r = __fmul_rn(__fmul_rn(expf(t), p.anchor_h[a]), p.stride);
-              else r = sigmoid_acc(t);
-              obase[(size_t)a * a_step + fi] = r;
+            if (ch0 + j < p.cout && valid && !(p.dbg & 256)) {                 // (ablation 256: no decoded stores)
+              if (staged) hs[(a * 32 + rank_v) * p.dec_cols + fi] = r[j];
+              else obase[(size_t)a * a_step + fi] = r[j];
             }
             if (++fi == p.dec_cols) { fi = 0; ++a; }
           }
+        }
+        if (staged && nvalid > 0 && !(p.dbg & 256)) {
+          __syncwarp();
+          const unsigned long long first = (unsigned long long)obase;
+          const unsigned long long b64 = ((unsigned long long)__shfl_sync(0xffffffffu, (unsigned)(first >> 32), lane0) << 32) |
+                                         (unsigned long long)__shfl_sync(0xffffffffu, (unsigned)first, lane0);
+          float* span = reinterpret_cast<float*>(b64);
+          const int nfl = nvalid * p.dec_cols;
+          for (int a = 0; a < p.n_anchors; ++a)
+            for (int i = lane; i < nfl; i += 32) span[(size_t)a * a_step + i] = hs[a * 32 * p.dec_cols + i];
+          __syncwarp();
         }
       }
       // this warp is done reading the accumulator: one arrival per warp on the LEADER's barrier
@@ -702,17 +737,17 @@ int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident) {
   return ((a_rows + 7) & ~7) * (int)kRowBytes + (resident ? 0 : G * (BN / 2) * (int)kRowBytes);
 }
 
-static int conv_gemm_fixed_smem(int num_stages, int nbuf) {
+static int conv_gemm_fixed_smem(int num_stages, int nbuf, int extra_bytes = 0) {
   (void)nbuf;
-  return 8 * (2 * num_stages + 2 * kMaxAcc + kEpiWarps * kMaxStageBufs + 2) + 32 +
+  return extra_bytes + 8 * (2 * num_stages + 2 * kMaxAcc + kEpiWarps * kMaxStageBufs + 2) + 32 +
          4 * kBiasFloats + 1024 /*alignment*/;
 }
 
 // -> stages (2..8) and staging buffers per epilogue warp (2 when they fit beside >= 3 stages, else 1)
-void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int* stages, int* nbuf) {
+void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int extra_bytes, int* stages, int* nbuf) {
   const int sb = units_per_stage * conv_gemm_stage_bytes(BN, G, a_rows, resident_bytes > 0);
   const int limit = 227 * 1024 - resident_bytes;
-  int s = (limit - conv_gemm_fixed_smem(8, 2)) / sb;
+  int s = (limit - conv_gemm_fixed_smem(8, 2, extra_bytes)) / sb;
   if (s > 8) s = 8;
   *stages = s;
   *nbuf = 2;      // kept for the plan's bookkeeping: the epilogue no longer stages through shared memory
@@ -731,7 +766,7 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
   }
   const int smem = (p.b_resident ? p.b_res_tiles * (p.BN / 2) * (int)kRowBytes : 0) +
                    p.num_stages * p.units_per_stage * conv_gemm_stage_bytes(p.BN, G, p.a_rows, p.b_resident) +
-                   conv_gemm_fixed_smem(p.num_stages, p.nbuf);
+                   conv_gemm_fixed_smem(p.num_stages, p.nbuf, kEpiWarps * p.head_stage_bytes);
   if (smem > 227 * 1024 || (p.b_resident && p.num_n_tiles != 1)) {
     set_error("conv_gemm: shared memory plan does not fit (%d bytes, resident=%d)", smem, p.b_resident);
     return AY_EINVAL;

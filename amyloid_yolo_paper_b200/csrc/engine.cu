@@ -109,6 +109,7 @@ struct Layer {
   int BN = 0, G = 1, a_rows = 128, stages = 0, nbuf = 1;
   int units_per_stage = 1;          // (group, k-block) units per pipeline stage
   int m_batch = 1;                  // 256-row blocks per tile (first layer: 4)
+  int head_stage_bytes = 0;         // head with <= 32 output channels: shared-memory staging of the decoded rows, per warp
   int b_resident = 0;               // weights stay in shared memory for the whole launch (single N tile, small K)
   int impl = 0;                     // 0 none, 1 tcgen05 gemm
   bool first = false;               // 3-channel first layer: GEMM over the staged 8-channel input x8
@@ -536,6 +537,10 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     if (L.is_head) L.BN = cout_p <= 256 ? cout_p : 256;
     else L.BN = (cout_p % 256 == 0) ? 256 : (cout_p % 128 == 0) ? 128 : (cout_p % 64 == 0) ? 64 : 32;
     L.cout_rows = ay::round_up(cout_p, L.BN);
+    if (L.is_head && cout_p == 32 && !getenv("AY_NO_HEADSTAGE")) {
+      const ay_layer_desc& Y = Ls[L.yolo_layer].d;
+      L.head_stage_bytes = (Y.n_anchors * 32 * (5 + Y.classes) * 4 + 15) & ~15;
+    }
     L.G = L.s2_packed ? 2 : (L.d.size == 3 && L.d.stride == 1 && !L.first) ? 3 : 1;
     // first layer: four 256-row blocks per tile (K is only 3 x 32: one barrier round and three loads per 1024 rows);
     // each CTA's box is its 512 consecutive pixels + shift + taps = 66 rows of 8 pixels
@@ -556,12 +561,12 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
         for (int u = 1; u <= units; ++u) {
           if (units % u != 0 || (u > 1 && (u * unit_bytes > 56 * 1024 || getenv("AY_ONE_UNIT")))) continue;
           int st = 0, nb = 0;
-          ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, rb, u, &st, &nb);
+          ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, rb, u, ay::kConvEpilogueWarps * L.head_stage_bytes, &st, &nb);
           if (st >= 3 && (u == 1 || nb == 2)) { best_u = u; best_st = st; best_nb = nb; }
         }
         if (best_u == 0 && pass == 1) {
           best_u = 1;
-          ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, 0, 1, &best_st, &best_nb);
+          ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, 0, 1, ay::kConvEpilogueWarps * L.head_stage_bytes, &best_st, &best_nb);
         }
         if (best_u > 0 && (pass == 1 || best_st >= 3)) {
           L.b_resident = pass == 0;
@@ -822,6 +827,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   q.prof = (ctx->profiling && ctx->prof_counters) ? ctx->prof_counters + (size_t)i * 16 : nullptr;
   if (L.is_head) {
     q.head = 1;
+    q.head_stage_bytes = L.head_stage_bytes;
     q.dec_out = dec_out; q.dec_rows_total = ctx->dec_rows; q.dec_row_off = Y->dec_row_off;
     q.dec_cols = ctx->dec_cols; q.n_anchors = Y->d.n_anchors; q.cout = L.C;
     const double stride = (double)ctx->img_size / (double)L.H;   // models.py:119

@@ -194,12 +194,14 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
                                      float orig_w, float orig_h, int merge, float* __restrict__ out_rows,
                                      int32_t* __restrict__ out_counts, TileScratch* scratch, unsigned int* err_flag) {
   const int b = blockIdx.x;
-  if (b >= batch || threadIdx.x != 0) return;
+  if (b >= batch) return;
+  const int lane = threadIdx.x;
   const int n = counts[b];
   const float* in = rows + (size_t)b * cap * 7;
   float* out = out_rows + (size_t)b * cap * 7;
-  if (n <= 0) { out_counts[b] = n < 0 ? n : 0; return; }
+  if (n <= 0) { if (lane == 0) out_counts[b] = n < 0 ? n : 0; return; }
   if (!merge || n > kMergeCap) {
+    if (lane != 0) return;
     if (merge) { atomicExch(err_flag, 0xCA9A0002u); out_counts[b] = -1; return; }
     for (int r = 0; r < n; ++r) {
       out[r * 7 + 0] = __fmul_rn(__fdiv_rn(__fsub_rn(in[r * 7 + 0], pad_x_half), unpad_w), orig_w);
@@ -233,9 +235,9 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
   Work* ts = &work;
   PySet live;
   live.init(ts);
-  int npool = 0, ngone = 0;
-  for (int r = 0; r < n; ++r) {
-    Entry& e = ts->pool[npool];
+  // rescale + tuple hash of the n detections: independent, one lane each (the FP64 hash is most of a small tile's time)
+  for (int r = lane; r < n; r += 32) {
+    Entry& e = ts->pool[r];
     e.v[0] = (double)__fmul_rn(__fdiv_rn(__fsub_rn(in[r * 7 + 0], pad_x_half), unpad_w), orig_w);
     e.v[1] = (double)__fmul_rn(__fdiv_rn(__fsub_rn(in[r * 7 + 1], pad_y_half), unpad_h), orig_h);
     e.v[2] = (double)__fmul_rn(__fdiv_rn(__fsub_rn(in[r * 7 + 2], pad_x_half), unpad_w), orig_w);
@@ -244,7 +246,12 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
     e.v[5] = (double)in[r * 7 + 5];
     e.v[6] = (double)in[r * 7 + 6];
     e.hash = hash_tuple7(e.v);
-    ts->gflag[npool] = 0;
+    ts->gflag[r] = 0;
+  }
+  __syncwarp();
+  if (lane != 0) return;              // the fixed point itself is serial (set iteration order)
+  int npool = 0, ngone = 0;
+  for (int r = 0; r < n; ++r) {
     live.add(npool);
     ++npool;   // duplicates stay in the pool but not in the set
   }

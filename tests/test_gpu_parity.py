@@ -411,3 +411,38 @@ def test_pipeline_end_to_end_vs_oracle_chain(dev):
     dxy = np.abs(dec_gpu[hi][:, :2] - ref32[hi][:, :2]).max()
     dwh = np.abs(np.log(dec_gpu[hi][:, 2:4] / ref32[hi][:, 2:4])).max()
     assert dxy <= 0.5 and dwh <= 2e-2, (dxy, dwh)      # centres within half a pixel of 416, sizes within 2 %
+
+
+@pytest.mark.parametrize("toggle", ["AY_NO_RESIDENT", "AY_NO_PACKED", "AY_NO_MBATCH", "AY_NO_UPFUSE", "AY_NO_HEADSTAGE",
+                                    "AY_ONE_UNIT"])
+def test_forward_plan_variants_agree(toggle, dev):
+    """Every planning shortcut of the convolution engine (resident weights, packed stride-2 operand, row-batched first
+    layer, fused upsample, staged head stores, multi-unit stages) can be switched off at ay_net_build time; the plain
+    plan must give the same network output (different summation order only)."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    cfg = ensure_cfg("yolov3-custom")
+    m, sd = _model(cfg, seed=3, conf_bias=-2.0, wh_gain=0.15)
+    blocks = R.parse_cfg(cfg)
+    tiles = torch.from_numpy(synth.synthetic_tiles(2, size=416, seed=11))
+    eng = m.engine(device=dev, max_batch=2)
+    base = eng.forward_u8(tiles).cpu()
+    eng.check()
+    m._engine = None                                    # force a new plan
+    os.environ[toggle] = "1"
+    try:
+        eng2 = m.engine(device=dev, max_batch=2)
+        other = eng2.forward_u8(tiles).cpu()
+        eng2.check()
+    finally:
+        del os.environ[toggle]
+        m._engine = None
+    x = torch.stack([R.preprocess_u8(t, 416) for t in tiles.numpy()])
+    with torch.no_grad():
+        _, raw32 = R.darknet_forward(blocks, sd, x, return_raw_heads=True)
+    raw_head_error(base, raw32, blocks)                 # (sets the grid sizes decoded_to_raw needs)
+    ra, rb = decoded_to_raw(base, blocks), decoded_to_raw(other, blocks)
+    worst = max(float(((a - b).abs() * (b.abs() < 12)).max() / b.abs().max()) for a, b in zip(ra, rb))
+    assert worst <= BF16_TOL, "%s: raw heads differ by %.3e" % (toggle, worst)
+    if toggle in ("AY_NO_UPFUSE", "AY_NO_HEADSTAGE", "AY_ONE_UNIT", "AY_NO_RESIDENT"):
+        assert np.array_equal(bits(base), bits(other)), "%s changes only data movement: results must be bit-identical" % toggle
