@@ -91,7 +91,11 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
                      cudaStream_t stream);
 int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident);
 void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int extra_bytes, int* stages, int* nbuf);
-constexpr int kConvEpilogueWarps = 8;
+#ifndef AY_EPI_PARTS
+#define AY_EPI_PARTS 2
+#endif
+constexpr int kConvEpilogueParts = AY_EPI_PARTS;            // epilogue warps per TMEM lane quarter (2 or 4)
+constexpr int kConvEpilogueWarps = 4 * kConvEpilogueParts;
 
 // aux_kernels.cu ------------------------------------------------------------
 struct FirstConvParams {

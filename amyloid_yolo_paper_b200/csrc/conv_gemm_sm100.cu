@@ -41,7 +41,8 @@ namespace ay {
 namespace {
 
 constexpr int kRowsPerCta = 128;
-constexpr int kEpiWarps = 8;
+constexpr int kEpiParts = kConvEpilogueParts;   // epilogue warps per TMEM lane quarter
+constexpr int kEpiWarps = kConvEpilogueWarps;
 constexpr int kThreads2 = 32 * (2 + kEpiWarps);   // producer, MMA issuer, 8 epilogue warps
 constexpr unsigned long long kSpinLimit = 6000000000ull;  // ~3 s: trap instead of hanging the GPU
 
@@ -168,7 +169,18 @@ __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + ex
 // ---- epilogue staging: 32 rows x 32 channels (64-byte rows, TMA SWIZZLE_64B layout), nbuf (1|2) buffers per warp ----
 constexpr uint32_t kStageBufBytes = 32 * 64;
 constexpr int kMaxStageBufs = 2;
-constexpr int kMaxChunksPerWarp = 4;     // BN <= 256: 8 chunks of 32 columns, two warps per TMEM lane quarter
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+  unsigned long long r, x = *reinterpret_cast<unsigned long long*>(&a), y = *reinterpret_cast<unsigned long long*>(&b);
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(x), "l"(y));
+  return *reinterpret_cast<float2*>(&r);
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  unsigned long long r, x = *reinterpret_cast<unsigned long long*>(&a), y = *reinterpret_cast<unsigned long long*>(&b);
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(x), "l"(y));
+  return *reinterpret_cast<float2*>(&r);
+}
+
+constexpr int kMaxChunksPerWarp = 8 / kEpiParts;     // BN <= 256: 8 chunks of 32 columns, two warps per TMEM lane quarter
 constexpr int kMaxAcc = 16;             // TMEM accumulators: 512 columns / BN
 constexpr int kBiasFloats = 1024;
 constexpr int kBK = 64;                 // channels per k-block: one 128-byte swizzle row
@@ -262,7 +274,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // all 512 TMEM columns (one CTA per SM): 512/BN accumulators, so that the MMA issuer runs that many tiles ahead
   // of the epilogue and the commit -> epilogue -> arrive round trip is off the critical path of small tiles
   const uint32_t tmem_cols = 512u;
-  const int num_acc = (p.dbg & 32) ? 2 : p.num_acc;
+  const int num_acc = (p.dbg & 32) ? kEpiParts : p.num_acc;
   const bool has_res = p.has_res && !(p.dbg & 8);
 
   if (warp == 0 && lane == 0) {
@@ -283,7 +295,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int a = 0; a < kMaxAcc; ++a) {
       bar_init(tfull_bar(a), 1);                // tcgen05.commit multicast
       // leader's copy: the epilogue warps of both CTAs that work on a tile (all 8, or 4 when BN = 32: see `split`)
-      bar_init(tempty_bar(a), tile_split ? kEpiWarps : 2 * kEpiWarps);
+      bar_init(tempty_bar(a), tile_split ? 8 : 2 * kEpiWarps);   // arrivals per accumulator, both CTAs
     }
     for (int w = 0; w < kEpiWarps; ++w)
       for (int b = 0; b < kMaxStageBufs; ++b) bar_init(res_bar(w, b), 1);   // residual TMA loads, per epilogue warp
@@ -464,7 +476,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ---------------- epilogue: warps 2..9; TMEM lane quarter = warp % 4, chunk parity = (warp-2)/4 ----------------
     const int ew = warp - 2;
     const int quarter = warp & 3;
-    const int half = ew >> 2;
+    const int part = ew >> 2;
     const int row_in_tile = quarter * 32 + lane;
     const uint32_t lane_addr = ((uint32_t)(quarter * 32)) << 16;
     const int hw = p.Hp * p.Wp;
@@ -476,15 +488,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // so tiles of up to four chunks are not shared between the two warps of a quarter: they take alternate TILES and
     // all chunks of their quarter, which keeps two tiles in flight per quarter and halves the per-tile fixed work.
     const bool split = tile_split;
-    const int c_first = split ? 0 : half;
-    const int c_step = split ? 1 : 2;
+    const int c_first = split ? 0 : part;
+    const int c_step = split ? 1 : kEpiParts;
     // Tile sequence of this warp and the row it owns in each tile, kept incrementally (tile -> (m tile, n tile) ->
     // (image, y, x) costs four integer divisions, ~100 dependent instructions, if recomputed per tile).
-    const int t_step = n_clusters * (split ? 2 : 1);
-    const int it_step = split ? 2 : 1;
+    const int t_step = n_clusters * (split ? kEpiParts : 1);
+    const int it_step = split ? kEpiParts : 1;
     const int nnt = p.num_n_tiles;
-    int tile = first_tile + (split ? half * n_clusters : 0);
-    int acc = (split ? half : 0) % num_acc;
+    int tile = first_tile + (split ? part * n_clusters : 0);
+    int acc = (split ? part : 0) % num_acc;
     uint32_t acc_phase = 0;
     int ntile = tile % nnt;
     int m = (tile / nnt) * tile_rows + (int)rank * kRowsPerCta * R + row_in_tile;
@@ -555,22 +567,25 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const long long mp = (long long)m + 2LL * qrows;
           if (nnt == 1 && mp < p.P) {
             const uint16_t* pf = static_cast<const uint16_t*>(p.res_ptr) + (size_t)mp * p.res_pitch;
-            for (int l = split ? 0 : half; l < (p.BN >> 6); l += c_step)
+            for (int l = split ? 0 : part; l < (p.BN >> 6); l += c_step)
               asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + l * 64) : "memory");
           }
         }
-        uint32_t res[kMaxChunksPerWarp][16];
-        if (has_res && in_range) {
-          const uint16_t* res_row = static_cast<const uint16_t*>(p.res_ptr) + (size_t)m * p.res_pitch + n0;
-#pragma unroll
-          for (int i = 0; i < kMaxChunksPerWarp; ++i) {
-            const int c = c_first + c_step * i;
-            if (c < nchunks) {
-              ldg256(res_row + c * 32, &res[i][0]);
-              ldg256(res_row + c * 32 + 16, &res[i][8]);
-            }
+        // The residual of chunk i is loaded two chunks ahead into a ring of two register buffers (the first two before
+        // the accumulator wait, so their latency hides behind the tile's MMAs): holding all four chunks' residuals
+        // at once (64 registers) made ptxas spill loop state of this hot path to local memory.
+        uint32_t res[2][16];
+        const uint16_t* res_row = static_cast<const uint16_t*>(p.res_ptr) + (size_t)m * p.res_pitch + n0;
+        const bool load_res = has_res && in_range;
+        auto load_residual = [&](int i) {
+          const int c = c_first + c_step * i;
+          if (load_res && c < nchunks) {
+            ldg256(res_row + c * 32, &res[i & 1][0]);
+            ldg256(res_row + c * 32 + 16, &res[i & 1][8]);
           }
-        }
+        };
+        load_residual(0);
+        if (kMaxChunksPerWarp > 1) load_residual(1);
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
         fence_after();
         const uint32_t t_acc = tmem_base + (uint32_t)(acc * acc_cols) + lane_addr;
@@ -590,31 +605,31 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               t = row_target(mr, image, py, px, (py == 0) | (py == p.Hp - 1) | (px == 0) | (px == p.Wp - 1));
               ch = 0;
             }
+            // fp32 pairs (add/mul.f32x2: FADD2 / FMUL2, same IEEE results as the scalar forms, half the instructions)
             const float4* bias4 = reinterpret_cast<const float4*>(s_bias + n0 + ch);
-            float f[32];
+            float2 f[16];
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
               const float4 bb = bias4[q];
-              f[4 * q + 0] = __uint_as_float(v[4 * q + 0]) + bb.x;
-              f[4 * q + 1] = __uint_as_float(v[4 * q + 1]) + bb.y;
-              f[4 * q + 2] = __uint_as_float(v[4 * q + 2]) + bb.z;
-              f[4 * q + 3] = __uint_as_float(v[4 * q + 3]) + bb.w;
+              f[2 * q + 0] = add2(make_float2(__uint_as_float(v[4 * q + 0]), __uint_as_float(v[4 * q + 1])), make_float2(bb.x, bb.y));
+              f[2 * q + 1] = add2(make_float2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])), make_float2(bb.z, bb.w));
             }
             if (p.leaky) {
 #pragma unroll
-              for (int e = 0; e < 32; ++e) f[e] = fmaxf(f[e], 0.1f * f[e]);   // == (x > 0 ? x : 0.1x) for every x
+              for (int e = 0; e < 16; ++e) {                     // max(x, 0.1x) == (x > 0 ? x : 0.1x) for every x
+                const float2 s = mul2(f[e], make_float2(0.1f, 0.1f));
+                f[e].x = fmaxf(f[e].x, s.x);
+                f[e].y = fmaxf(f[e].y, s.y);
+              }
             }
             uint32_t o[16];
 #pragma unroll
             for (int e = 0; e < 16; ++e) {
-              float lo = f[2 * e], hi = f[2 * e + 1];
-              if (has_res) {
-                const float2 rr = unpack_pair<FP16>(res[i][e]);
-                lo += rr.x;
-                hi += rr.y;
-              }
-              o[e] = t.zero ? 0u : pack_pair<FP16>(lo, hi);
+              float2 y = f[e];
+              if (has_res) y = add2(y, unpack_pair<FP16>(res[i & 1][e]));
+              o[e] = t.zero ? 0u : pack_pair<FP16>(y.x, y.y);
             }
+            if (i + 2 < kMaxChunksPerWarp) load_residual(i + 2);
             if (p.up_mode) {
               if (t.up && !(p.dbg & 4)) {
                 const size_t down = (size_t)(2 * (p.Wp - 2) + 2) * p.out_pitch;      // one row of the upsampled grid
