@@ -530,11 +530,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // and a proxy fence per chunk and made the epilogue, not the tensor pipe, the bound of the 3x3 layers.)
         // Chunk c of a tile is 32 accumulator columns: channels c*32.. of the tile's rows, or - for row-batched tiles
         // (m_batch > 1, BN = 32) - all 32 channels of the rows of sub-block c.
-        struct RowTarget { bool store, zero, up; uint16_t* out; uint16_t* plane; };
+        struct RowTarget { bool store, up; uint16_t* out; uint16_t* plane; };
         auto row_target = [&](int mr, int image, int py, int px, bool is_halo) {
           RowTarget t;
-          t.store = mr < p.P;
-          t.zero = is_halo | !t.store;
+          // halo rows are never written: every output buffer (rows and planes) is zero-filled when the plan allocates it
+          // and each padded pixel owns its row, so the halo stays zero without a select per value and a store per row
+          t.store = (mr < p.P) & !is_halo;
           t.out = static_cast<uint16_t*>(p.out_ptr) + (size_t)mr * p.out_pitch + n0;
           t.plane = nullptr;
           t.up = false;
@@ -542,7 +543,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // nearest x2 upsample fused (models.py:86-96): interior pixel (py, px) fills the 2x2 block whose top-left
             // padded coordinate is (2py-1, 2px-1) of the consumer's [2H+2, 2W+2] grid; halo rows write nothing
             const int Wt = 2 * (p.Wp - 2) + 2, Ht = 2 * (p.Hp - 2) + 2;
-            t.up = t.store && !is_halo;
+            t.up = t.store;
             t.out = static_cast<uint16_t*>(p.out_ptr) + (((size_t)image * Ht + (2 * py - 1)) * Wt + (2 * px - 1)) * p.out_pitch + n0;
           }
           if (p.plane_mode != 0) {
@@ -576,7 +577,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // at once (64 registers) made ptxas spill loop state of this hot path to local memory.
         uint32_t res[2][16];
         const uint16_t* res_row = static_cast<const uint16_t*>(p.res_ptr) + (size_t)m * p.res_pitch + n0;
-        const bool load_res = has_res && in_range;
+        const bool load_res = has_res && in_range && !halo;
         auto load_residual = [&](int i) {
           const int c = c_first + c_step * i;
           if (load_res && c < nchunks) {
@@ -627,7 +628,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int e = 0; e < 16; ++e) {
               float2 y = f[e];
               if (has_res) y = add2(y, unpack_pair<FP16>(res[i & 1][e]));
-              o[e] = t.zero ? 0u : pack_pair<FP16>(y.x, y.y);
+              o[e] = pack_pair<FP16>(y.x, y.y);
             }
             if (i + 2 < kMaxChunksPerWarp) load_residual(i + 2);
             if (p.up_mode) {
