@@ -490,8 +490,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool split = tile_split;
     const int c_first = split ? 0 : part;
     const int c_step = split ? 1 : kEpiParts;
-    // Tile sequence of this warp and the row it owns in each tile, kept incrementally (tile -> (m tile, n tile) ->
-    // (image, y, x) costs four integer divisions, ~100 dependent instructions, if recomputed per tile).
+    // Tile sequence of this warp and the row it owns in each tile.
     const int t_step = n_clusters * (split ? kEpiParts : 1);
     const int it_step = split ? kEpiParts : 1;
     const int nnt = p.num_n_tiles;
@@ -500,23 +499,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t acc_phase = 0;
     int ntile = tile % nnt;
     int m = (tile / nnt) * tile_rows + (int)rank * kRowsPerCta * R + row_in_tile;
-    int img = m / hw;
-    int yy = (m - img * hw) / p.Wp;
-    int xx = m - img * hw - yy * p.Wp;
     const int dq = t_step / nnt, dr = t_step - dq * nnt;       // tile += t_step  ==  (m tile, n tile) += (dq, dr) with carry
     const int qrows = dq * tile_rows;
-    const int qI = qrows / hw, qY = (qrows - qI * hw) / p.Wp, qX = qrows - qI * hw - qY * p.Wp;
-    const int tI = tile_rows / hw, tY = (tile_rows - tI * hw) / p.Wp, tX = tile_rows - tI * hw - tY * p.Wp;
-    auto advance_row = [&](int dI, int dY, int dX) {
-      xx += dX;
-      if (xx >= p.Wp) { xx -= p.Wp; ++yy; }
-      yy += dY;
-      if (yy >= p.Hp) { yy -= p.Hp; ++img; }
-      img += dI;
+    // row -> (image, y, x) of the padded grid by multiply-shift with host-computed reciprocals (exact for every row of the
+    // launch, see magic_div): six instructions per tile and no carried state (the incremental form kept nine more
+    // registers live across the tile loop, which ptxas spilled to local memory on this path)
+    auto split_row = [&](int row, int& image, int& py, int& px) {
+      image = (int)(((unsigned long long)(unsigned)row * p.div_hw_mul) >> p.div_hw_shift);
+      const int rem = row - image * hw;
+      py = (int)(((unsigned long long)(unsigned)rem * p.div_wp_mul) >> p.div_wp_shift);
+      px = rem - py * p.Wp;
     };
     for (; tile < total_tiles; tile += t_step) {
       const int n0 = ntile * p.BN;
       const bool in_range = m < p.P;
+      int img, yy, xx;
+      split_row(m, img, yy, xx);
       const bool halo = (yy == 0) | (yy == p.Hp - 1) | (xx == 0) | (xx == p.Wp - 1);
 
       if (p.dbg & 64) {                                          // ablation: no epilogue work at all
@@ -600,9 +598,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             int ch = c * 32;
             if (R > 1) {                                         // sub-block c of a row-batched tile: 128 rows further per c
               const int mr = m + c * kRowsPerCta;
-              int px = xx + c * kRowsPerCta, py = yy, image = img;   // (no divisions: c * 128 < 4 rows of the image)
-              while (px >= p.Wp) { px -= p.Wp; ++py; }
-              if (py >= p.Hp) { py -= p.Hp; ++image; }
+              int px, py, image;
+              split_row(mr, image, py, px);
               t = row_target(mr, image, py, px, (py == 0) | (py == p.Hp - 1) | (px == 0) | (px == p.Wp - 1));
               ch = 0;
             }
@@ -728,11 +725,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (acc >= num_acc) { acc -= num_acc; acc_phase ^= 1u; }
       ntile += dr;
       m += qrows;
-      advance_row(qI, qY, qX);
       if (ntile >= nnt) {
         ntile -= nnt;
         m += tile_rows;
-        advance_row(tI, tY, tX);
       }
     }
   }
@@ -769,9 +764,31 @@ void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int unit
   *nbuf = 2;      // kept for the plan's bookkeeping: the epilogue no longer stages through shared memory
 }
 
+// floor(n / d) == (n * mul) >> shift for every n < 2^nbits:  shift = nbits + ceil(log2 d), mul = ceil(2^shift / d)
+// (mul * d - 2^shift < d <= 2^ceil(log2 d), so the error term n * (mul*d - 2^shift) / (d * 2^shift) stays below 1/d)
+static void magic_div(unsigned d, int nbits, unsigned* mul, int* shift) {
+  int lg = 0;
+  while ((1ull << lg) < d) ++lg;
+  *shift = nbits + lg;
+  *mul = (unsigned)(((1ull << *shift) + d - 1) / d);
+}
+
 int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
-                     const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
+                     const CUtensorMap& tmResPF, const ConvGemmParams& p_in, int G, int is_fp16, int num_sms,
                      cudaStream_t stream) {
+  ConvGemmParams p = p_in;
+  {
+    // rows reach P rounded up to whole tiles (plus the row batch of the last one)
+    const unsigned long long max_row = (unsigned long long)p.num_m_tiles * 256ull * (unsigned)p.m_batch + 1024ull;
+    int nbits = 1;
+    while ((1ull << nbits) <= max_row) ++nbits;
+    const unsigned hw = (unsigned)p.Hp * (unsigned)p.Wp;
+    int lg_hw = 0;
+    while ((1ull << lg_hw) < hw) ++lg_hw;
+    if (nbits > 30) { set_error("conv_gemm: %llu rows exceed the row-index range", max_row); return AY_EINVAL; }
+    magic_div(hw, nbits, &p.div_hw_mul, &p.div_hw_shift);
+    magic_div((unsigned)p.Wp, lg_hw, &p.div_wp_mul, &p.div_wp_shift);     // remainder < Hp*Wp <= 2^lg_hw
+  }
   if (p.BN % 32 != 0 || p.BN < 32 || p.BN > 256 || p.num_stages < 2 || p.num_stages > 8 || (G != 1 && G != 2 && G != 3) ||
       (p.nbuf != 1 && p.nbuf != 2) || p.num_n_tiles * p.BN > kBiasFloats || p.units_per_stage < 1 ||
       p.m_batch < 1 || (p.m_batch > 1 && (p.BN != 32 || p.head || p.has_res || p.m_batch > 8)) ||

@@ -142,10 +142,17 @@ class TileDetector:
             self._counts_h = [torch.empty((self.max_batch,), dtype=torch.int32).pin_memory() for _ in range(2)]
             self._rows_h = [torch.empty((self.max_batch, self.cap, 7), dtype=torch.float32).pin_memory() for _ in range(2)]
         big = self.max_batch if self.max_batch < 128 else self.max_batch // 2
+        plan = getattr(self, "sub_batches", None)        # explicit sub-batch sizes of one max_batch (tuning / tests)
         spans, lo = [], 0
         while lo < n:
             left = n - lo
-            if self.max_batch >= 128 and lo % self.max_batch == 0 and left > big // 2:
+            if plan:
+                k, acc = 0, 0
+                while k < len(plan) - 1 and acc + plan[k] <= lo % self.max_batch:
+                    acc += plan[k]
+                    k += 1
+                size = min(int(plan[k]), big)
+            elif self.max_batch >= 128 and lo % self.max_batch == 0 and left > big // 2:
                 size = big // 4                      # first sub-batch of a batch: short, its upload is exposed
             elif self.max_batch >= 128 and lo % self.max_batch == big // 4:
                 size = big - big // 4
