@@ -63,6 +63,7 @@ struct ConvGemmParams {
   int nbuf;              // epilogue staging buffers per warp (1 or 2)
   int Hp, Wp;            // padded output size (halo test)
   unsigned div_hw_mul, div_wp_mul; int div_hw_shift, div_wp_shift;   // filled by launch_conv_gemm: row / (Hp*Wp), rem / Wp
+  int epi_dr, epi_qrows;                                             // filled by launch_conv_gemm: tile step of an epilogue warp
   const float* bias;     // [num_n_tiles*BN]
   int has_res;           // residual tile added after the activation (shortcut fused)
   void* out_ptr; int out_pitch;          // output rows (16-bit elements), channel 0 of this layer's slice

@@ -25,13 +25,18 @@
 // whose upper half is out of bounds and therefore zero-filled by the hardware.
 //
 // Kernel shape: persistent, one CTA per SM, clusters of 2, 320 threads per CTA:
-//   warp 0   : TMA producer (one lane, in both CTAs; all loads signal the LEADER's full barrier)
-//   warp 1   : tcgen05.mma issuer (one lane, leader CTA only); tcgen05.commit multicast to both CTAs
-//   warps 2-9: epilogue, two warps per TMEM lane quarter (tcgen05.ld 32x32b.x32), alternating 32-column
-//              chunks, so that every scheduler has two epilogue warps to hide each other's latencies
-// TMEM holds two BN-column accumulators so the epilogue of tile i overlaps the main loop of i+1.
-// All global traffic of the epilogue goes through the TMA (residual tile in, result tile out): a
-// thread-per-row ld/st.global touches 32 lines per warp instruction and serialises in the LSU.
+//   warp 0   : TMA producer (all lanes converged, the copies predicated by elect.sync, in both CTAs; every load
+//              signals the LEADER's full barrier)
+//   warp 1   : tcgen05.mma issuer (leader CTA only, same converged form); tcgen05.commit multicast to both CTAs
+//   warps 2-9: epilogue, two warps per TMEM lane quarter (tcgen05.ld 32x32b.x32).  Tiles of up to four 32-column
+//              chunks are taken whole by alternate warps of a quarter (two tiles in flight per quarter), wider
+//              tiles are split by alternate chunks.
+// TMEM holds 512 / (BN * m_batch) accumulators, so the issuer runs that many tiles ahead of the epilogue.
+// The epilogue is thread = output row: residual in and result out are 256-bit ld/st.global straight from/to
+// registers (one 32-byte sector per thread and instruction), the math runs on fp32 pairs (FADD2/FMUL2), halo rows
+// are never written (the plan zero-fills every buffer once).  An earlier version staged both directions through
+// TMA boxes in shared memory; its load round trip, store drain and proxy fence per chunk were the bound of the
+// 3x3 layers.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -226,7 +231,7 @@ __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
 }
 
 // G = taps per pipeline stage (3: the kw taps of one kh share one 130-row A box; 1: one tap per stage)
-template <int G, bool FP16>
+template <int G, bool FP16, bool SPLIT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes,
@@ -247,7 +252,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int tile_rows = 2 * kRowsPerCta * R;
   const int acc_cols = p.BN * R;
   // tiles of <= 4 chunks (32 accumulator columns each): the two epilogue warps of a TMEM lane quarter take alternate tiles
-  const bool tile_split = (acc_cols >> 5) == 1 || ((acc_cols >> 5) <= kMaxChunksPerWarp && !p.head);
+  // (SPLIT: chosen by launch_conv_gemm - a single chunk, or up to kMaxChunksPerWarp chunks of a non-head layer)
+  constexpr bool tile_split = SPLIT;
   const uint32_t unit_bytes = a_region + (p.b_resident ? 0u : G * b_tile);
   const uint32_t stage_bytes = (uint32_t)U * unit_bytes;
   const uint32_t tx_bytes = (uint32_t)U * ((uint32_t)p.a_rows * kRowBytes + (p.b_resident ? 0u : G * b_tile));   // one CTA's loads per stage
@@ -487,20 +493,20 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // The epilogue of one warp is a long dependent instruction stream (~550 instructions per tile and chunk at IPC ~0.2),
     // so tiles of up to four chunks are not shared between the two warps of a quarter: they take alternate TILES and
     // all chunks of their quarter, which keeps two tiles in flight per quarter and halves the per-tile fixed work.
-    const bool split = tile_split;
+    constexpr bool split = SPLIT;
     const int c_first = split ? 0 : part;
-    const int c_step = split ? 1 : kEpiParts;
+    constexpr int c_step = split ? 1 : kEpiParts;
     // Tile sequence of this warp and the row it owns in each tile.
     const int t_step = n_clusters * (split ? kEpiParts : 1);
-    const int it_step = split ? kEpiParts : 1;
+    constexpr int it_step = split ? kEpiParts : 1;
     const int nnt = p.num_n_tiles;
     int tile = first_tile + (split ? part * n_clusters : 0);
     int acc = (split ? part : 0) % num_acc;
     uint32_t acc_phase = 0;
     int ntile = tile % nnt;
     int m = (tile / nnt) * tile_rows + (int)rank * kRowsPerCta * R + row_in_tile;
-    const int dq = t_step / nnt, dr = t_step - dq * nnt;       // tile += t_step  ==  (m tile, n tile) += (dq, dr) with carry
-    const int qrows = dq * tile_rows;
+    // tile += t_step  ==  (m tile, n tile) += (dq, dr) with carry; qrows = dq * tile_rows (host-computed: kept in the
+    // constant bank instead of registers that ptxas would spill across the tile loop)
     // row -> (image, y, x) of the padded grid by multiply-shift with host-computed reciprocals (exact for every row of the
     // launch, see magic_div): six instructions per tile and no carried state (the incremental form kept nine more
     // registers live across the tile loop, which ptxas spilled to local memory on this path)
@@ -563,7 +569,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (has_res) {
           // pull this thread's residual row of its tile two steps ahead into L2 (single-N-tile layers: the small tiles
           // whose MMAs are too short to hide an HBM round trip)
-          const long long mp = (long long)m + 2LL * qrows;
+          const long long mp = (long long)m + 2LL * p.epi_qrows;
           if (nnt == 1 && mp < p.P) {
             const uint16_t* pf = static_cast<const uint16_t*>(p.res_ptr) + (size_t)mp * p.res_pitch;
             for (int l = split ? 0 : part; l < (p.BN >> 6); l += c_step)
@@ -723,8 +729,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // next tile of this warp
       acc += it_step;
       if (acc >= num_acc) { acc -= num_acc; acc_phase ^= 1u; }
-      ntile += dr;
-      m += qrows;
+      ntile += p.epi_dr;
+      m += p.epi_qrows;
       if (ntile >= nnt) {
         ntile -= nnt;
         m += tile_rows;
@@ -807,15 +813,28 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
   const int total = p.num_m_tiles * p.num_n_tiles;
   const int pairs = num_sms / 2;
   const int grid = 2 * (total < pairs ? total : pairs);
-#define AY_LAUNCH(GG, FF)                                                                                              \
-  do {                                                                                                                 \
-    AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<GG, FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));  \
-    conv_gemm_kernel<GG, FF><<<grid, kThreads2, smem, stream>>>(tmA, tmB, tmOut, tmRes, tmResPF, p);                   \
+  // epilogue schedule: tiles of one chunk, or of up to kMaxChunksPerWarp chunks in a non-head layer, are taken whole
+  // by alternate warps of a TMEM lane quarter (SPLIT); wider tiles are shared chunk by chunk
+  const int chunks = (p.BN * p.m_batch) >> 5;
+  const bool split = chunks == 1 || (chunks <= kMaxChunksPerWarp && !p.head);
+  if (split && (p.num_acc % kEpiParts) != 0) { set_error("conv_gemm: %d accumulators cannot be shared by tile", p.num_acc); return AY_EINVAL; }
+  {
+    const int t_step = (grid / 2) * (split ? kEpiParts : 1);
+    const int dq = t_step / p.num_n_tiles;
+    p.epi_dr = t_step - dq * p.num_n_tiles;
+    p.epi_qrows = dq * 256 * p.m_batch;
+  }
+#define AY_LAUNCH3(GG, FF, SS)                                                                                             \
+  do {                                                                                                                     \
+    AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<GG, FF, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));  \
+    conv_gemm_kernel<GG, FF, SS><<<grid, kThreads2, smem, stream>>>(tmA, tmB, tmOut, tmRes, tmResPF, p);                   \
   } while (0)
+#define AY_LAUNCH(GG, FF) do { if (split) AY_LAUNCH3(GG, FF, true); else AY_LAUNCH3(GG, FF, false); } while (0)
   if (G == 3) { if (is_fp16) AY_LAUNCH(3, true); else AY_LAUNCH(3, false); }
   else if (G == 2) { if (is_fp16) AY_LAUNCH(2, true); else AY_LAUNCH(2, false); }
   else        { if (is_fp16) AY_LAUNCH(1, true); else AY_LAUNCH(1, false); }
 #undef AY_LAUNCH
+#undef AY_LAUNCH3
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

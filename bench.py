@@ -66,6 +66,17 @@ def measured_peaks():
     return {"bf16": 1400.0, "bf16_burst": 1590.0, "hbm": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def profiled_traffic(batch):
+    """DRAM bytes of the conv stack per ay_forward, from the committed ncu capture (profiles/*_conv_traffic.json,
+    tools/traffic_json.py), scaled per tile; None when no capture is committed."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_conv_traffic.json")))
+    if not files:
+        return None, None
+    d = json.load(open(files[-1]))
+    return float(d["bytes_per_tile"]) * batch, os.path.basename(files[-1])
+
+
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -345,6 +356,7 @@ def main():
         peaks = measured_peaks()
         flop = FLOP_PER_TILE[args.net]
         achieved = B * flop / (fwd_mean * 1e-3) / 1e12
+        traffic, traffic_src = profiled_traffic(B)
         line = {
             "metric": METRIC, "value": world * B * K / (ms * 1e-3), "unit": "tiles/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -356,7 +368,8 @@ def main():
             "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
                        "samples": clk["samples"]},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16"], "unit": "TFLOP/s",
-                         "frac": achieved / peaks["bf16"], "traffic": None,
+                         "frac": achieved / peaks["bf16"], "traffic": traffic, "traffic_unit": "DRAM bytes per ay_forward",
+                         "traffic_source": traffic_src,
                          "kernel": "conv stack (ay_forward: %d launches, tcgen05 implicit GEMM)" % fwd_launches,
                          "ms": fwd_mean, "flop_per_tile": flop, "peak_source": peaks["source"],
                          "frac_of_burst": achieved / peaks["bf16_burst"]},
