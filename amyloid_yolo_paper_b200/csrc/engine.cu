@@ -552,7 +552,8 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       const int res_bytes = (L.BN / 2) * L.ktot * 2;
       const int n_groups = L.first ? 3 : L.d.size == 1 ? 1 : (L.d.stride == 1 || L.s2_packed) ? 3 : 9;
       const int units = n_groups * (L.s2_packed ? 1 : L.cin_k / 64);
-      const bool try_res = L.cout_rows == L.BN && res_bytes <= 96 * 1024 && !getenv("AY_NO_RESIDENT");
+      const int res_cap = (getenv("AY_RES_KB") ? atoi(getenv("AY_RES_KB")) : 96) * 1024;
+      const bool try_res = L.cout_rows == L.BN && res_bytes <= res_cap && !getenv("AY_NO_RESIDENT");
       L.units_per_stage = 1;
       for (int pass = try_res ? 0 : 1; pass < 2 && L.stages == 0; ++pass) {
         const int rb = pass == 0 ? res_bytes : 0;
