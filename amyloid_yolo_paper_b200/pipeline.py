@@ -130,17 +130,13 @@ class TileDetector:
             out.append(rows_h[b, :k].clone() if k > 0 else None)
 
     def _detect_host(self, tiles, original_shape):
-        """Host input.  Sub-batches are uploaded on a copy stream into two device buffers while the previous one
-        computes (a small first sub-batch keeps the exposed part of the H2D short); results come back on a third
-        stream from two result slots, so the compute stream never waits for the host between sub-batches."""
-        n = tiles.shape[0]
-        main = torch.cuda.current_stream(self.device)
-        if getattr(self, "_copy_stream", None) is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-            self._d2h_stream = torch.cuda.Stream(device=self.device)
-            self._stage = [None, None]
-            self._counts_h = [torch.empty((self.max_batch,), dtype=torch.int32).pin_memory() for _ in range(2)]
-            self._rows_h = [torch.empty((self.max_batch, self.cap, 7), dtype=torch.float32).pin_memory() for _ in range(2)]
+        """Host input, one call: the stream below over a single batch."""
+        return next(self.detect_stream([tiles], original_shape))
+
+    def _plan_spans(self, n, stream_head=True):
+        """Sub-batches of one host batch of n tiles: (lo, hi) spans.  At the head of a stream a short first sub-batch of
+        every max_batch keeps the exposed part of the first upload short; later batches of a stream upload under the
+        previous batch's compute and use full-size sub-batches only."""
         big = self.max_batch if self.max_batch < 128 else self.max_batch // 2
         plan = getattr(self, "sub_batches", None)        # explicit sub-batch sizes of one max_batch (tuning / tests)
         spans, lo = [], 0
@@ -151,65 +147,111 @@ class TileDetector:
                 while k < len(plan) - 1 and acc + plan[k] <= lo % self.max_batch:
                     acc += plan[k]
                     k += 1
-                size = min(int(plan[k]), big)
-            elif self.max_batch >= 128 and lo % self.max_batch == 0 and left > big // 2:
-                size = big // 4                      # first sub-batch of a batch: short, its upload is exposed
-            elif self.max_batch >= 128 and lo % self.max_batch == big // 4:
+                size = min(int(plan[k]), self.max_batch)
+            elif not stream_head:
+                size = self.max_batch                # steady state of a stream: whole batches, fewest waves wasted
+            elif stream_head and self.max_batch >= 128 and lo % self.max_batch == 0 and left > big // 2:
+                size = big // 4
+            elif stream_head and self.max_batch >= 128 and lo % self.max_batch == big // 4:
                 size = big - big // 4
             else:
                 size = big
             spans.append((lo, min(n, lo + size)))
             lo = spans[-1][1]
-        shape = (big,) + tuple(tiles.shape[1:])
-        for i in range(2):
-            if self._stage[i] is None or self._stage[i].shape != shape or self._stage[i].dtype != tiles.dtype:
-                self._stage[i] = torch.empty(shape, dtype=tiles.dtype, device=self.device)
-        copied = [torch.cuda.Event() for _ in spans]
-        computed = [torch.cuda.Event() for _ in spans]
-        fetched = [None] * len(spans)
+        return spans
 
-        def upload(i):
-            lo, hi = spans[i]
+    def detect_stream(self, batches, original_shape=None):
+        """``batches``: iterable of HOST tensors (ideally pinned; uint8 [B,H,H,3] or fp32 [B,3,S,S], any B each) - what
+        ``detect.py:88-95`` pulls from its DataLoader.  Yields, per batch and in order, the list ``detect()`` returns.
+
+        One software pipeline runs across the whole iterable: sub-batches are uploaded on a copy stream into two device
+        buffers while the previous one computes, results come back on a third stream from two result slots and are
+        unpacked on the host one sub-batch behind the compute - so the upload of batch k+1 and the read-back of batch k-1
+        overlap the compute of batch k, and only the first upload and the last read-back of the stream are exposed."""
+        main = torch.cuda.current_stream(self.device)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._d2h_stream = torch.cuda.Stream(device=self.device)
+            self._stage = [None, None]
+            self._counts_h = [torch.empty((self.max_batch,), dtype=torch.int32).pin_memory() for _ in range(2)]
+            self._rows_h = [torch.empty((self.max_batch, self.cap, 7), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.d2h_bytes = 0
+
+        def work():                                   # (batch index, tiles, lo, hi, last span of its batch)
+            for bi, tiles in enumerate(batches):
+                if tiles.is_cuda:
+                    raise ValueError("detect_stream takes host batches; use detect() for device tensors")
+                spans = self._plan_spans(tiles.shape[0], stream_head=(bi == 0))
+                for k, (lo, hi) in enumerate(spans):
+                    yield bi, tiles, lo, hi, k == len(spans) - 1
+                if not spans:
+                    yield bi, tiles, 0, 0, True
+
+        copied, computed, fetched = {}, {}, {}
+
+        def upload(i, item):
+            _, tiles, lo, hi, _ = item
+            shape = (self.max_batch,) + tuple(tiles.shape[1:])
+            buf = self._stage[i % 2]
+            if buf is None or buf.shape != shape or buf.dtype != tiles.dtype:
+                torch.cuda.synchronize(self.device)          # (first use or a new tile shape: rare)
+                buf = self._stage[i % 2] = torch.empty(shape, dtype=tiles.dtype, device=self.device)
             with torch.cuda.stream(self._copy_stream):
-                if i >= 2:
+                if i - 2 in computed:
                     self._copy_stream.wait_event(computed[i - 2])    # the compute that read this buffer has finished
-                self._stage[i % 2][:hi - lo].copy_(tiles[lo:hi], non_blocking=True)
-                copied[i].record(self._copy_stream)
+                if hi > lo:
+                    buf[:hi - lo].copy_(tiles[lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+                copied[i] = ev
 
-        def fetch(i):            # D2H of slot i % 2 on its own stream, after the compute of sub-batch i
-            lo, hi = spans[i]
+        def fetch(i, n):         # D2H of slot i % 2 on its own stream, after the compute of span i
             with torch.cuda.stream(self._d2h_stream):
                 self._d2h_stream.wait_event(computed[i])
-                self._counts_h[i % 2][:hi - lo].copy_(self._out_counts[i % 2][:hi - lo], non_blocking=True)
-                self._rows_h[i % 2][:hi - lo].copy_(self._out_rows[i % 2][:hi - lo], non_blocking=True)
+                self._counts_h[i % 2][:n].copy_(self._out_counts[i % 2][:n], non_blocking=True)
+                self._rows_h[i % 2][:n].copy_(self._out_rows[i % 2][:n], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(self._d2h_stream)
                 fetched[i] = ev
+            self.d2h_bytes += n * (4 + self.cap * 28)        # counts + padded rows copied back
 
-        def collect(i, out):
-            lo, hi = spans[i]
+        def collect(i, n, out):
             fetched[i].synchronize()
-            counts = self._counts_h[i % 2][:hi - lo].tolist()
-            if min(counts) < 0:
+            counts = self._counts_h[i % 2][:n].tolist()
+            if counts and min(counts) < 0:
                 self.check()                         # raises the capacity error with its message
             rows_h = self._rows_h[i % 2]
             for b, k in enumerate(counts):
                 out.append(rows_h[b, :k].clone() if k > 0 else None)
+            for d in (copied, computed, fetched):
+                d.pop(i - 2, None)
 
-        out = []
-        self.d2h_bytes = sum((hi - lo) * (4 + self.cap * 28) for lo, hi in spans)    # counts + padded rows copied back
-        upload(0)
-        for i, (lo, hi) in enumerate(spans):
-            if i + 1 < len(spans):
-                upload(i + 1)
+        it = work()
+        cur = next(it, None)
+        if cur is not None:
+            upload(0, cur)
+        i, prev, out = 0, None, []
+        while cur is not None:
+            nxt = next(it, None)
+            if nxt is not None:
+                upload(i + 1, nxt)
+            n = cur[3] - cur[2]
             main.wait_event(copied[i])
-            if i >= 2:
+            if i - 2 in fetched:
                 main.wait_event(fetched[i - 2])      # result slot i % 2 has been read back
-            self.run_device(self._stage[i % 2][:hi - lo], original_shape, slot=i % 2)
-            computed[i].record(main)
-            fetch(i)
-            if i >= 1:
-                collect(i - 1, out)
-        collect(len(spans) - 1, out)
-        self.check()
-        return out
+            if n > 0:
+                self.run_device(self._stage[i % 2][:n], original_shape, slot=i % 2)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            computed[i] = ev
+            fetch(i, n)
+            if prev is not None:
+                collect(i - 1, prev[3] - prev[2], out)
+                if prev[4]:
+                    yield out
+                    out = []
+            prev, cur, i = cur, nxt, i + 1
+        if prev is not None:
+            collect(i - 1, prev[3] - prev[2], out)
+            self.check()
+            yield out

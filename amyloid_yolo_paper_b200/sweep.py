@@ -11,6 +11,8 @@ the final gather of per-tile detection lists —
 over NCCL (NVLink/NVSwitch) on the GPU box, gloo in the CPU tests.  No activation or
 weight traffic; each rank holds a full weight replica.
 """
+import itertools
+
 import torch
 import torch.distributed as dist
 
@@ -84,8 +86,15 @@ def sweep(detector, tile_source, n_tiles, batch, group=None, gather=True):
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     lo, hi = shard_range(n_tiles, rank, world)
     per_tile = []
-    for b0 in range(lo, hi, batch):
-        per_tile.extend(detector.detect(tile_source(b0, min(hi, b0 + batch))))
+    batches = (tile_source(b0, min(hi, b0 + batch)) for b0 in range(lo, hi, batch))
+    first = next(batches, None)
+    if first is not None and not first.is_cuda:
+        # host tiles: one software pipeline over the whole shard (upload of batch k+1 under the compute of batch k)
+        for outs in detector.detect_stream(itertools.chain([first], batches)):
+            per_tile.extend(outs)
+    elif first is not None:
+        for tiles in itertools.chain([first], batches):
+            per_tile.extend(detector.detect(tiles))
     dev = detector.device if (dist.is_initialized() and dist.get_backend(group) == "nccl") else None
     rows, counts = pack_detections(per_tile, device=dev)
     if gather and world > 1:

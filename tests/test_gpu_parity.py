@@ -446,3 +446,34 @@ def test_forward_plan_variants_agree(toggle, dev):
     assert worst <= BF16_TOL, "%s: raw heads differ by %.3e" % (toggle, worst)
     if toggle in ("AY_NO_UPFUSE", "AY_NO_HEADSTAGE", "AY_ONE_UNIT", "AY_NO_RESIDENT"):
         assert np.array_equal(bits(base), bits(other)), "%s changes only data movement: results must be bit-identical" % toggle
+
+
+@pytest.mark.gpu
+def test_detect_stream_equals_per_batch_detect(dev):
+    """The streaming host path (one pipeline across batches, uneven sub-batches, ragged last batch, an empty batch)
+    returns exactly what one synchronous detect() per batch returns."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    cfg = ensure_cfg("yolov3-custom")
+    m, _ = _model(cfg, seed=1, conf_bias=(-6.0, -1.5, -6.0), wh_gain=0.15)
+    det = TileDetector(m, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=8, cap=512, device=dev)
+    det.sub_batches = [2, 3, 3]
+    sizes = [8, 5, 0, 8, 1]
+    batches = [torch.from_numpy(synth.synthetic_tiles(n, size=640, seed=20 + i)).pin_memory() if n else
+               torch.empty((0, 640, 640, 3), dtype=torch.uint8) for i, n in enumerate(sizes)]
+    want = [det.detect(b.to(dev)) if b.shape[0] else [] for b in batches]
+    got = list(det.detect_stream(batches))
+    assert [len(g) for g in got] == sizes
+    n_det = 0
+    for gb, wb in zip(got, want):
+        for g, w in zip(gb, wb):
+            assert (g is None) == (w is None)
+            if g is not None:
+                assert torch.equal(g.view(torch.int32), w.view(torch.int32))
+                n_det += len(g)
+    assert n_det > 0
+    # the single-call host path is the same stream over one batch
+    one = det.detect(batches[1])
+    for g, w in zip(one, want[1]):
+        assert (g is None) == (w is None) and (g is None or torch.equal(g, w))
