@@ -49,6 +49,7 @@ struct ConvGemmParams {
   int num_n_tiles;       // Cout_padded / BN
   int n_groups;          // A boxes per k-block
   int kb_per_tap;        // ceil(Cin / 64)
+  int k16_all, k16_last; // K=16 MMA steps of a 64-channel k-block that hold data: all taps of a group / its last tap (0 = 4)
   int a_row_off[9];      // row offset of group g's A box
   int b_tap0[9];         // first weight tap of group g (K layout is tap-major)
   int a_rows;            // rows of the A box (128, or 130 with tap reuse)

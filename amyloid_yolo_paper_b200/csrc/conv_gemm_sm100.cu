@@ -405,6 +405,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int acc = 0;
       uint32_t acc_phase = 0;
       const uint32_t b_step = p.b_resident ? (uint32_t)p.kb_per_tap * (b_tile >> 4) : (b_tile >> 4);   // tap j+1 of a group
+      const int k16_all = p.k16_all > 0 ? p.k16_all : kBK / 16, k16_last = p.k16_last > 0 ? p.k16_last : kBK / 16;
       if (p.b_resident) {
         bar_wait(bres_bar, 0u, p.err_flag, 6);
         __syncwarp();
@@ -452,12 +453,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
               } else {
                 const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFFu);
+                // a 32-channel input fills only the first two K=16 steps of its 64-channel block (the rest is the TMA's
+                // zero fill against zero weights): those MMAs are not issued
 #pragma unroll
                 for (int j = 0; j < G; ++j) {
+                  const int ks = j == G - 1 ? k16_last : k16_all;
 #pragma unroll
                   for (int k = 0; k < kBK / 16; ++k)
-                    umma2_f16(d_tmem, a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k), b0 + (uint64_t)(j * b_step + 2 * k), idesc,
-                              first | (uint32_t)(j | k));
+                    if (k < ks)
+                      umma2_f16(d_tmem, a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k), b0 + (uint64_t)(j * b_step + 2 * k), idesc,
+                                first | (uint32_t)(j | k));
                 }
               }
             }

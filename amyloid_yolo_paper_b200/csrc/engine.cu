@@ -776,6 +776,11 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   q.num_n_tiles = L.cout_rows / L.BN;
   q.a_rows = L.a_rows;
   q.kb_per_tap = L.cin_k / 64;
+  q.k16_all = q.k16_last = 4;
+  if (!getenv("AY_FULL_K")) {
+    if (!L.first && !L.s2_packed && L.cin_p == 32) q.k16_all = q.k16_last = 2;   // upper half of the k-block: zero weights
+    if (L.s2_packed) q.k16_last = 2;                                             // [kw2 | 0]
+  }
   if (L.first) {
     q.n_groups = 3;                       // one group per kh; K of a group = the 3 pixels x 8 channels of that row
     q.kb_per_tap = 1;
