@@ -167,7 +167,8 @@ __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
 template <bool FP16>
 __device__ __forceinline__ float2 unpack_pair(uint32_t w) {
   if (FP16) return __half22float2(*reinterpret_cast<__half2*>(&w));
-  return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
+  // bf16 -> fp32 is a 16-bit shift: two ALU ops per pair (the library conversion compiles to PRMT + two IMAD.U32)
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
 }
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 
