@@ -7,6 +7,8 @@ mkdir -p $O
 MINE='regex:conv_gemm_kernel|prep_input_kernel|nms_|rescale_merge_kernel|s2_gather_kernel|upsample2_kernel|add_kernel|copy_channels_kernel|maxpool_kernel'
 timeout 300 python bench.py --steps 20 --warmup 3 > $O/bench.log 2> $O/bench.err; echo bench=$?
 timeout 200 python tools/layer_times.py --batch 256 --reps 5 --counters --out $O/layer_times.txt > $O/lt.log 2>&1; echo lt=$?
+# ablation floors per layer: full | no epilogue work (dbg 64) | no output stores (dbg 4)
+timeout 200 python tools/layer_times.py --batch 256 --reps 5 --dbg 0,64,4 --out $O/layer_ablation.txt > $O/abl.log 2>&1; echo abl=$?
 timeout 120 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/bench_short.log 2>&1; echo short=$?
 # launch list of our kernels over the same command (cold-cache, serialised: shares, not absolutes)
 timeout 400 ncu --metrics gpu__time_duration.sum --clock-control none -k "$MINE" -c 900 --csv \
