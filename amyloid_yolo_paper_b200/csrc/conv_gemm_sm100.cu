@@ -471,6 +471,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (++kb == p.kb_per_tap) { kb = 0; ++g; }
           }
           if (el) umma2_commit(empty_bar(stage));   // frees this stage in both CTAs
+          if (el && (p.dbg & 128)) umma2_commit(dummy_bar);   // ablation: what one more commit costs the issuing thread
           __syncwarp();
           if (prof) { pc[3] += c2 - c1; pc[4] += clock64() - c2; pc[7] += 1; }
           if (++stage == S) { stage = 0; phase ^= 1u; }
@@ -541,32 +542,41 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // Chunk c of a tile is 32 accumulator columns: channels c*32.. of the tile's rows, or - for row-batched tiles
         // (m_batch > 1, BN = 32) - all 32 channels of the rows of sub-block c.
         struct RowTarget { bool store, up; uint16_t* out; uint16_t* plane; };
+        // Addresses: 32-bit row indices (every buffer has < 2^31 rows, checked by the plan) and ONE 32x32->64-bit multiply
+        // by the row pitch in bytes per target; size_t arithmetic throughout cost ~90 instructions per call, which the
+        // row-batched first layer pays per chunk.
+        auto at = [](void* base, uint32_t row, uint32_t row_bytes, uint32_t extra_bytes) {
+          return reinterpret_cast<uint16_t*>(static_cast<char*>(base) + ((unsigned long long)row * row_bytes + extra_bytes));
+        };
+        const uint32_t n0b = (uint32_t)n0 * 2u;
         auto row_target = [&](int mr, int image, int py, int px, bool is_halo) {
           RowTarget t;
           // halo rows are never written: every output buffer (rows and planes) is zero-filled when the plan allocates it
           // and each padded pixel owns its row, so the halo stays zero without a select per value and a store per row
           t.store = (mr < p.P) & !is_halo;
-          t.out = static_cast<uint16_t*>(p.out_ptr) + (size_t)mr * p.out_pitch + n0;
           t.plane = nullptr;
           t.up = false;
           if (p.up_mode) {
             // nearest x2 upsample fused (models.py:86-96): interior pixel (py, px) fills the 2x2 block whose top-left
             // padded coordinate is (2py-1, 2px-1) of the consumer's [2H+2, 2W+2] grid; halo rows write nothing
-            const int Wt = 2 * (p.Wp - 2) + 2, Ht = 2 * (p.Hp - 2) + 2;
+            // (their index below wraps and is never dereferenced)
+            const uint32_t Wt = 2u * (uint32_t)(p.Wp - 2) + 2u, Ht = 2u * (uint32_t)(p.Hp - 2) + 2u;
             t.up = t.store;
-            t.out = static_cast<uint16_t*>(p.out_ptr) + (((size_t)image * Ht + (2 * py - 1)) * Wt + (2 * px - 1)) * p.out_pitch + n0;
+            const uint32_t row = ((uint32_t)image * Ht + (uint32_t)(2 * py - 1)) * Wt + (uint32_t)(2 * px - 1);
+            t.out = at(p.out_ptr, row, (uint32_t)p.out_pitch * 2u, n0b);
+          } else {
+            t.out = at(p.out_ptr, (uint32_t)mr, (uint32_t)p.out_pitch * 2u, n0b);
           }
           if (p.plane_mode != 0) {
             // padded output pixel (py, px) -> plane (py&1, px&1), position (py/2 + 1, px/2 + 1) of the half-size padded grid
-            const int Hq2 = (p.Hp - 2) / 2 + 2, Wq2 = (p.Wp - 2) / 2 + 2;
-            const size_t pos = ((size_t)image * Hq2 + (py >> 1) + 1) * Wq2 + (px >> 1) + 1;
+            const uint32_t Hq2 = (uint32_t)(p.Hp - 2) / 2u + 2u, Wq2 = (uint32_t)(p.Wp - 2) / 2u + 2u;
+            const uint32_t pos = ((uint32_t)image * Hq2 + (uint32_t)(py >> 1) + 1u) * Wq2 + (uint32_t)(px >> 1) + 1u;
+            const uint32_t prow_n = (uint32_t)p.plane_rows, pitch_b = (uint32_t)p.plane_pitch * 2u;
             if (p.plane_packed) {
               // row-parity plane, 2 x pitch channels per row: [pixel with even padded x | pixel with odd padded x]
-              t.plane = static_cast<uint16_t*>(p.planes) + ((size_t)(py & 1) * (size_t)p.plane_rows + pos) * (2 * p.plane_pitch) +
-                        (px & 1) * p.plane_pitch + n0;
+              t.plane = at(p.planes, (uint32_t)(py & 1) * prow_n + pos, 2u * pitch_b, (uint32_t)(px & 1) * pitch_b + n0b);
             } else {
-              const size_t prow = (size_t)((py & 1) * 2 + (px & 1)) * (size_t)p.plane_rows + pos;
-              t.plane = static_cast<uint16_t*>(p.planes) + prow * p.plane_pitch + n0;
+              t.plane = at(p.planes, (uint32_t)((py & 1) * 2 + (px & 1)) * prow_n + pos, pitch_b, n0b);
             }
           }
           return t;
@@ -577,7 +587,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           // whose MMAs are too short to hide an HBM round trip)
           const long long mp = (long long)m + 2LL * p.epi_qrows;
           if (nnt == 1 && mp < p.P) {
-            const uint16_t* pf = static_cast<const uint16_t*>(p.res_ptr) + (size_t)mp * p.res_pitch;
+            const uint16_t* pf = at(const_cast<void*>(p.res_ptr), (uint32_t)mp, (uint32_t)p.res_pitch * 2u, 0u);
             for (int l = split ? 0 : part; l < (p.BN >> 6); l += c_step)
               asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + l * 64) : "memory");
           }
@@ -586,7 +596,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // the accumulator wait, so their latency hides behind the tile's MMAs): holding all four chunks' residuals
         // at once (64 registers) made ptxas spill loop state of this hot path to local memory.
         uint32_t res[2][16];
-        const uint16_t* res_row = static_cast<const uint16_t*>(p.res_ptr) + (size_t)m * p.res_pitch + n0;
+        const uint16_t* res_row = at(const_cast<void*>(p.res_ptr), (uint32_t)m, (uint32_t)p.res_pitch * 2u, n0b);
         const bool load_res = has_res && in_range && !halo;
         auto load_residual = [&](int i) {
           const int c = c_first + c_step * i;
