@@ -140,6 +140,26 @@ struct DecodeParams {
 };
 int launch_decode(const DecodeParams& p, cudaStream_t s);
 
+// fp32_path.cu (act_dtype = AY_F32: fp32 storage, CUDA-core FFMA accumulation) ------------------
+struct F32PrepParams {
+  const void* in; int in_kind; int batch; int S; int src_h, src_w;
+  const int* idx_y; const int* idx_x;
+  float* out;                                 // [B,S+2,S+2,3]
+};
+struct F32ConvParams {
+  const float* in; int in_pitch; int Cin; int H, W;   // zero-haloed NHWC input (unpadded H,W)
+  const float* w;                                     // [size*size*Cin][Cout], K order (kh,kw,c)
+  const float* bias; int Cout; int size, stride, leaky;
+  float* out; int out_pitch; int Ho, Wo; int batch;
+};
+int launch_f32_prep(const F32PrepParams& p, cudaStream_t s);
+int launch_f32_conv(const F32ConvParams& p, cudaStream_t s);
+int launch_f32_maxpool(const float* in, int C, int batch, int H, int W, int size, int stride, float* out, cudaStream_t s);
+int launch_f32_upsample2(const float* in, int C, int batch, int H, int W, float* out, cudaStream_t s);
+int launch_f32_add(const float* a, const float* b, long long n, float* out, cudaStream_t s);
+int launch_f32_copy_channels(const float* in, int C, long long rows, float* out, int out_pitch, cudaStream_t s);
+int launch_f32_dump_nchw(const float* in, int C, int batch, int H, int W, float* out, cudaStream_t s);
+
 // nms.cu / merge.cu -----------------------------------------------------------
 struct NmsScratch {
   void* buf = nullptr; size_t bytes = 0;

@@ -141,6 +141,9 @@ struct Layer {
   std::vector<int> copy_srcs;       // sources that must be copied into the concat buffer
   std::vector<int> copy_offs;
   bool fused_into_prev = false;     // shortcut handled by the previous conv
+  // fp32 accuracy mode (AY_F32, fp32_path.cu): zero-haloed NHWC fp32 rows, pitch = C; weights [K][Cout]
+  float* f_out = nullptr;
+  float* f_w = nullptr;
 };
 
 }  // namespace
@@ -154,6 +157,8 @@ struct ay_ctx {
   std::vector<ay::Layer> layers;
   int in_channels = 3, img_size = 416, max_batch = 0, is_fp16 = 0;
   bool built = false, finalized = false, use_ref = false;
+  bool is_f32 = false;                // AY_F32 network: every block runs the fp32 kernels of fp32_path.cu
+  float* f_in = nullptr;              // AY_F32: staged input [B,S+2,S+2,3]
   int dbg = 0;                        // AY_DBG ablation bits (see ConvGemmParams::dbg)
   int dec_rows = 0, dec_cols = 0;
   int* idx_y = nullptr;               // nearest-resize tables (device), rebuilt when the source size changes
@@ -311,7 +316,7 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
                             int max_batch, int act_dtype) {
   AY_ENTER(ctx);
   if (!descs || n_layers <= 0 || max_batch <= 0 || img_size <= 0 || img_size % 32 != 0 ||
-      (act_dtype != AY_BF16 && act_dtype != AY_FP16)) {
+      (act_dtype != AY_BF16 && act_dtype != AY_FP16 && act_dtype != AY_F32)) {
     set_error("ay_net_build: bad arguments (n_layers=%d max_batch=%d img_size=%d dtype=%d)", n_layers, max_batch,
               img_size, act_dtype);
     return AY_EINVAL;
@@ -322,6 +327,8 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
   ctx->img_size = img_size;
   ctx->max_batch = max_batch;
   ctx->is_fp16 = act_dtype == AY_FP16;
+  ctx->is_f32 = act_dtype == AY_F32;
+  ctx->f_in = nullptr;
   ctx->layers.resize(n_layers);
   std::vector<Layer>& Ls = ctx->layers;
 
@@ -398,6 +405,40 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     pc = L.C; ph = L.H; pw = L.W;
   }
   if (ctx->dec_rows == 0) { set_error("network has no [yolo] block"); return AY_EINVAL; }
+
+  // ---- fp32 accuracy mode: one buffer per block, no fusion
+  if (ctx->is_f32) {
+    if (in_channels != 3) { set_error("fp32 mode: the input must have 3 channels"); return AY_EINVAL; }
+    AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->f_in),
+                         sizeof(float) * (size_t)ay::padded_rows(max_batch, img_size, img_size) * 3, true));
+    for (int i = 0; i < n_layers; ++i) {
+      Layer& L = Ls[i];
+      const size_t elems = (size_t)ay::padded_rows(max_batch, L.H, L.W) * L.C;
+      switch (L.d.type) {
+        case AY_CONV:
+          L.impl = 4;
+          AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_w), sizeof(float) * (size_t)L.d.size * L.d.size * L.cin * L.C, false));
+          AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.C, true));
+          AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_out), sizeof(float) * elems, true));
+          break;
+        case AY_ROUTE:
+          if (L.d.n_src == 1) { L.f_out = Ls[L.d.src[0]].f_out; break; }
+          AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_out), sizeof(float) * elems, true));
+          break;
+        case AY_YOLO:
+          L.f_out = Ls[i - 1].f_out;
+          break;
+        default:
+          AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_out), sizeof(float) * elems, true));
+          break;
+      }
+    }
+    AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_y), sizeof(int) * img_size, true));
+    AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_x), sizeof(int) * img_size, true));
+    AY_CUDA(cudaDeviceSynchronize());
+    ctx->built = true;
+    return AY_OK;
+  }
 
   // ---- pass 2: fusion decisions
   for (int i = 0; i < n_layers; ++i) {
@@ -624,6 +665,17 @@ extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const flo
   }
   Layer& L = ctx->layers[layer];
   const int k = L.d.size, taps = k * k, cout = L.C, cin = L.cin;
+  if (ctx->is_f32) {
+    std::vector<float> r((size_t)taps * cin * cout);          // OIHW -> [(kh,kw,c)][o]
+    for (int o = 0; o < cout; ++o)
+      for (int c = 0; c < cin; ++c)
+        for (int t = 0; t < taps; ++t) r[((size_t)t * cin + c) * cout + o] = w[((size_t)o * cin + c) * taps + t];
+    AY_CUDA(cudaMemcpy(L.f_w, r.data(), r.size() * sizeof(float), cudaMemcpyHostToDevice));
+    AY_CUDA(cudaMemcpy(L.bias, bias, sizeof(float) * cout, cudaMemcpyHostToDevice));
+    L.weights_set = true;
+    ctx->finalized = false;
+    return AY_OK;
+  }
   if (L.first) {
     std::vector<float> r((size_t)cout * 27);
     std::vector<uint16_t> r16((size_t)L.cout_rows * L.ktot, 0);
@@ -720,6 +772,76 @@ void nearest_table(int dst, int src, std::vector<int>* out) {
     int s = (int)floorf((float)i * scale);
     (*out)[i] = s < src - 1 ? s : src - 1;
   }
+}
+
+// AY_F32 networks: the cfg blocks one by one (models.py:237-255), every tensor in fp32
+int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w, float* dec_out,
+                cudaStream_t st) {
+  std::vector<Layer>& Ls = ctx->layers;
+  ay::F32PrepParams pp{};
+  pp.in = input; pp.in_kind = in_kind; pp.batch = batch; pp.S = ctx->img_size; pp.src_h = src_h; pp.src_w = src_w;
+  pp.idx_y = ctx->idx_y; pp.idx_x = ctx->idx_x; pp.out = ctx->f_in;
+  AY_TRY(ay::launch_f32_prep(pp, st));
+  ++ctx->launches;
+  for (int i = 0; i < (int)Ls.size(); ++i) {
+    Layer& L = Ls[i];
+    if (ctx->profiling) AY_CUDA(cudaEventRecord(ctx->prof_events[i], st));
+    const float* prev = i ? Ls[i - 1].f_out : ctx->f_in;
+    const int pC = i ? Ls[i - 1].C : 3, pH = i ? Ls[i - 1].H : ctx->img_size, pW = i ? Ls[i - 1].W : ctx->img_size;
+    switch (L.d.type) {
+      case AY_CONV: {
+        ay::F32ConvParams q{};
+        q.in = prev; q.in_pitch = pC; q.Cin = L.cin; q.H = pH; q.W = pW;
+        q.w = L.f_w; q.bias = L.bias; q.Cout = L.C; q.size = L.d.size; q.stride = L.d.stride; q.leaky = L.d.leaky;
+        q.out = L.f_out; q.out_pitch = L.C; q.Ho = L.H; q.Wo = L.W; q.batch = batch;
+        AY_TRY(ay::launch_f32_conv(q, st));
+        ++ctx->launches;
+        break;
+      }
+      case AY_MAXPOOL:
+        AY_TRY(ay::launch_f32_maxpool(prev, pC, batch, pH, pW, L.d.size, L.d.stride, L.f_out, st));
+        ++ctx->launches;
+        break;
+      case AY_UPSAMPLE:
+        AY_TRY(ay::launch_f32_upsample2(prev, pC, batch, pH, pW, L.f_out, st));
+        ++ctx->launches;
+        break;
+      case AY_ROUTE:
+        if (L.d.n_src > 1) {
+          int off = 0;
+          for (int k = 0; k < L.d.n_src; ++k) {
+            const Layer& S = Ls[L.d.src[k]];
+            AY_TRY(ay::launch_f32_copy_channels(S.f_out, S.C, ay::padded_rows(batch, S.H, S.W), L.f_out + off, L.C, st));
+            ++ctx->launches;
+            off += S.C;
+          }
+        }
+        break;
+      case AY_SHORTCUT:
+        AY_TRY(ay::launch_f32_add(prev, Ls[L.d.src[0]].f_out, ay::padded_rows(batch, L.H, L.W) * L.C, L.f_out, st));
+        ++ctx->launches;
+        break;
+      case AY_YOLO: {
+        ay::DecodeParams d{};
+        d.raw = prev; d.raw_pitch = pC; d.batch = batch; d.G = L.H; d.n_anchors = L.d.n_anchors;
+        d.dec_cols = ctx->dec_cols;
+        const double stride = (double)ctx->img_size / (double)L.H;      // models.py:119
+        d.stride = (float)stride;
+        for (int a = 0; a < L.d.n_anchors; ++a) {
+          d.anchor_w[a] = (float)((double)L.d.anchors[2 * a] / stride);  // models.py:122-124
+          d.anchor_h[a] = (float)((double)L.d.anchors[2 * a + 1] / stride);
+        }
+        d.dec_out = dec_out; d.dec_rows_total = ctx->dec_rows; d.dec_row_off = L.dec_row_off;
+        AY_TRY(ay::launch_decode(d, st));
+        ++ctx->launches;
+        break;
+      }
+      default:
+        break;
+    }
+  }
+  if (ctx->profiling) AY_CUDA(cudaEventRecord(ctx->prof_events[Ls.size()], st));
+  return AY_OK;
 }
 
 int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int src_h, int src_w, float* dec_out,
@@ -898,6 +1020,7 @@ extern "C" int ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch
     return AY_EINVAL;
   }
   ctx->launches = 0;
+  if (ctx->is_f32) return forward_f32(ctx, input, in_kind, batch, src_h, src_w, out_decoded, st);
   std::vector<Layer>& Ls = ctx->layers;
   for (int i = 0; i < (int)Ls.size(); ++i) {
     Layer& L = Ls[i];
@@ -993,6 +1116,10 @@ extern "C" int ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out
     return AY_EINVAL;
   }
   const Layer& L = ctx->layers[layer];
+  if (ctx->is_f32) {
+    if (!L.f_out) { set_error("layer %d has no stored output", layer); return AY_EINVAL; }
+    return ay::launch_f32_dump_nchw(L.f_out, L.C, batch, L.H, L.W, out_nchw, static_cast<cudaStream_t>(stream));
+  }
   if (!L.out.ptr || (!ctx->use_ref && L.up_consumer >= 0)) {
     set_error("layer %d is fused into its consumer and has no stored output", layer);
     return AY_EINVAL;

@@ -106,7 +106,7 @@ class Engine:
         if code != 0:
             raise _lib.EngineUnavailable(self.lib.ay_last_error().decode())
         descs = build_layer_descs(module_defs)
-        dtype = {"bf16": _lib.AY_BF16, "fp16": _lib.AY_FP16}[precision]
+        dtype = {"bf16": _lib.AY_BF16, "fp16": _lib.AY_FP16, "fp32": _lib.AY_F32}[precision]
         with torch.cuda.device(self.index):
             _lib.check(self.lib.ay_net_build(self.ctx, descs, len(module_defs), self.in_channels, self.img_size,
                                              self.max_batch, dtype))

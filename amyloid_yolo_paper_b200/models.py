@@ -109,7 +109,9 @@ class Darknet(nn.Module):
         self._engine = None           # built lazily on first forward (needs a GPU)
         self._engine_key = None
         self._weights_epoch = 0
-        self.precision = "bf16"       # activation storage of the tensor-core path: "bf16" | "fp16"
+        # "bf16" | "fp16": activation storage of the tensor-core path (2e-2 bar on the raw heads);
+        # "fp32": the accuracy mode, fp32 storage + FFMA accumulation on the CUDA cores (1e-4 bar)
+        self.precision = "bf16"
 
     # ------------------------------------------------------------------ engine
     def engine(self, device=None, max_batch=None):

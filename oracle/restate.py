@@ -104,6 +104,8 @@ def darknet_forward(blocks, state, x, emulate_bf16=False, return_layers=False, r
     hyper, defs = blocks[0], blocks[1:]
     img_dim = x.shape[2]
     outs, yolo, raws = [], [], []
+    # a float64 input evaluates the whole network in float64 (tests use it to size the fp32 noise floor)
+    ft = torch.float64 if (x.dtype == torch.float64 and not emulate_bf16) else torch.float32
 
     def q(t):
         return t.to(torch.bfloat16).to(torch.float32) if emulate_bf16 else t
@@ -112,15 +114,15 @@ def darknet_forward(blocks, state, x, emulate_bf16=False, return_layers=False, r
         t = d["type"]
         if t == "convolutional":
             k = int(d["size"])
-            w = state[_conv_key(i, "conv", "weight")].float()
+            w = state[_conv_key(i, "conv", "weight")].to(ft)
             bn = int(d["batch_normalize"])
             if bn:
-                g = state[_conv_key(i, "batch_norm", "weight")].float()
-                b = state[_conv_key(i, "batch_norm", "bias")].float()
-                mu = state[_conv_key(i, "batch_norm", "running_mean")].float()
-                var = state[_conv_key(i, "batch_norm", "running_var")].float()
+                g = state[_conv_key(i, "batch_norm", "weight")].to(ft)
+                b = state[_conv_key(i, "batch_norm", "bias")].to(ft)
+                mu = state[_conv_key(i, "batch_norm", "running_mean")].to(ft)
+                var = state[_conv_key(i, "batch_norm", "running_var")].to(ft)
             else:
-                cb = state[_conv_key(i, "conv", "bias")].float()
+                cb = state[_conv_key(i, "conv", "bias")].to(ft)
             if emulate_bf16:
                 if bn:
                     s = g / torch.sqrt(var + 1e-5)

@@ -281,6 +281,82 @@ def test_forward_full_networks_vs_oracle(name, batch, dev):
     assert worst <= BF16_TOL, "tcgen05 vs CUDA-core convolution, raw heads: %.3e" % worst
 
 
+FP32_TOL = 1e-4          # north_star: raw head outputs within 1e-4 relative in the FP32 mode
+
+
+def test_forward_fp32_mode_mini_vs_reference_golden(golden, dev):
+    """precision = "fp32" (fp32 storage, FFMA accumulation) against the reference's own Darknet.forward output."""
+    g = golden("forward_mini_ref.npz")
+    with tempfile.TemporaryDirectory() as d:
+        cfg = write_mini_cfg(d)
+        m, sd = _model(cfg, seed=0, conf_bias=-1.0, img_size=64)
+        m.precision = "fp32"
+        y = m(torch.from_numpy(g["x"]))
+        want = torch.from_numpy(g["y"])
+        assert y.shape == want.shape and not y.is_cuda
+        assert rel_max(y, want) <= FP32_TOL
+        assert float(((y - want).abs() / want.abs().clamp_min(1e-3)).max()) <= 1e-3      # elementwise as well
+        eng = m.engine(device=dev, max_batch=2)
+        assert eng.precision == "fp32"
+        y8 = eng.forward_u8(torch.from_numpy(g["tiles"])).cpu()                           # u8 / 255 + nearest resize
+        eng.check()
+        assert rel_max(y8, want) <= FP32_TOL
+        for i, dsc in enumerate(m.module_defs):
+            if dsc["type"] == "convolutional":
+                assert eng.layer_impl(i) == 4, "fp32 networks run the fp32 CUDA-core convolution"
+
+
+@pytest.mark.parametrize("name,batch", [("yolov3-custom", 2), ("yolov3-tiny", 3)])
+def test_forward_fp32_mode_full_networks_vs_oracle(name, batch, dev):
+    """The 1e-4 bar: RAW head outputs of the fp32 mode (read from the head convolutions' stored outputs, not
+    recovered through the decode) and every stored layer output vs the fp32 oracle; decoded rows as well."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    cfg = ensure_cfg(name)
+    m, sd = _model(cfg, seed=1, conf_bias=-2.0)
+    m.precision = "fp32"
+    blocks = R.parse_cfg(cfg)
+    tiles = synth.synthetic_tiles(batch, size=640, seed=3)
+    x = torch.stack([R.preprocess_u8(t, 416) for t in tiles])
+    with torch.no_grad():
+        ref32, raw32 = R.darknet_forward(blocks, sd, x, return_raw_heads=True)
+        _, ref_layers = R.darknet_forward(blocks, sd, x, return_layers=True)
+        _, raw64 = R.darknet_forward(blocks, sd, x.double(), return_raw_heads=True)
+    eng = m.engine(device=dev, max_batch=batch)
+    got = eng.forward_u8(torch.from_numpy(tiles)).cpu()
+    eng.check()
+    assert got.shape == ref32.shape and torch.isfinite(got).all()
+    heads = [i - 1 for i, dsc in enumerate(blocks[1:]) if dsc["type"] == "yolo"]
+    assert len(heads) == len(raw32)
+    for i, want, want64 in zip(heads, raw32, raw64):
+        raw = eng.layer_output(i, batch).cpu()
+        assert raw.shape == want.shape
+        assert rel_max(raw, want) <= FP32_TOL, "raw head %d: %.3e" % (i, rel_max(raw, want))
+        # elementwise, 99.9th percentile (SURVEY 8d; values below 1 % of the head's range are measured against that
+        # floor).  Truth is the oracle evaluated in float64: the fp32 oracle itself sits 4-6e-5 from it on this metric
+        # (summation order), so two fp32 evaluations may differ by the sum of their floors.
+        def p999(a, b):
+            q = ((a.double() - b.double()).abs() / b.double().abs().clamp_min(1e-2 * float(b.abs().max()))).flatten()
+            return float(torch.quantile(q[:: max(1, q.numel() // 1000000)], 0.999))
+        e64, e32, o32 = p999(raw, want64), p999(raw, want), p999(want, want64)
+        print("fp32 mode, head at layer %d: rel_max vs fp32 oracle %.3e, vs fp64 oracle %.3e; elementwise p99.9 vs fp64 %.3e, "
+              "vs fp32 %.3e (fp32 oracle vs fp64: %.3e)" % (i, rel_max(raw, want), rel_max(raw.double(), want64), e64, e32, o32))
+        assert rel_max(raw.double(), want64) <= FP32_TOL
+        assert e64 <= 2 * FP32_TOL
+        assert e32 <= 3 * FP32_TOL
+    assert rel_max(got, ref32) <= FP32_TOL
+    assert rel_max(got[..., 4:], ref32[..., 4:]) <= FP32_TOL
+    worst = 0.0
+    for i, dsc in enumerate(blocks[1:]):
+        if dsc["type"] == "yolo":
+            continue
+        worst = max(worst, rel_max(eng.layer_output(i, batch).cpu(), ref_layers[i]))
+    assert worst <= FP32_TOL, "per-layer activations vs fp32 oracle: %.3e" % worst
+    # same tiles through the caller's float contract (Darknet.forward): identical bits to the u8 entry
+    y = m(x)
+    assert np.array_equal(bits(y), bits(got))
+
+
 def test_forward_batch_invariance_and_ragged_batches(dev):
     """A tile's result does not depend on its batch neighbours or position (B=1 vs B=7 slices)."""
     from amyloid_yolo_paper_b200 import synth
