@@ -129,6 +129,17 @@ def test_layer_desc_struct_matches_header():
     assert ctypes.sizeof(_lib.LayerDesc) == size
 
 
+def test_precision_enum_matches_header():
+    """The host's activation-type constants are the header's (bf16 / fp16 tensor-core path, fp32 accuracy mode)."""
+    text = open(_lib.HEADER).read()
+    enum = re.search(r"enum \{ (AY_BF16 = \d+, AY_FP16 = \d+, AY_F32 = \d+) \};", text).group(1)
+    vals = dict((k.strip(), int(v)) for k, v in (kv.split("=") for kv in enum.split(",")))
+    assert vals == {"AY_BF16": _lib.AY_BF16, "AY_FP16": _lib.AY_FP16, "AY_F32": _lib.AY_F32}
+    from amyloid_yolo_paper_b200.models import Darknet
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    assert Darknet(ensure_cfg("yolov3-tiny")).precision == "bf16"        # the tensor-core path is the default
+
+
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
 def test_product_fails_loudly_without_gpu(tmp_path):
     """No CPU fallback anywhere on the product path."""
