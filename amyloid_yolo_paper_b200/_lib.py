@@ -98,6 +98,9 @@ _PROTOTYPES = {
     "ay_forward_profile": [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                            ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_float), ctypes.c_int],
     "ay_debug_set": [ctypes.c_void_p, ctypes.c_int],
+    "ay_prof_words": [],
+    "ay_forward_stamps": [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                          ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_ulonglong), ctypes.c_int],
     "ay_debug_counters": [ctypes.c_void_p, ctypes.POINTER(ctypes.c_ulonglong), ctypes.c_int],
 }
 

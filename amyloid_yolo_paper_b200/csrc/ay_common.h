@@ -81,17 +81,22 @@ struct ConvGemmParams {
   int plane_packed;      // 32-channel producer: the column-parity pair shares one 64-channel row of a ROW-parity plane
   // fused YOLO decode (head convolutions)
   int head;
+  int head_fast;         // 3 anchors x 7 columns in one chunk: compile-time channel roles, MUFU exp / reciprocal
   int head_stage_bytes;  // per epilogue warp: n_anchors * 32 * dec_cols floats when the head fits one 32-column chunk, else 0
   float* dec_out;        // [B, dec_rows_total, dec_cols]
   int dec_rows_total, dec_row_off, dec_cols, n_anchors, cout;
   float stride;
   float anchor_w[8], anchor_h[8];   // already divided by stride (models.py:122)
   unsigned int* err_flag;
-  unsigned long long* prof;   // 16 cycle counters of CTA 0 (profiling runs only), else nullptr
+  unsigned long long* prof;   // kProfWords counters (profiling runs only), else nullptr: [0..15] cycle counters of CTA 0,
+                              // then %globaltimer stamps of every CTA: entry, end of prologue, exit, dependency resolved
+  int pdl;                    // launch with programmatic stream serialization (prologue overlaps the previous layer's tail)
 };
-int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
-                     const CUtensorMap& tmResPF, const ConvGemmParams& p, int G, int is_fp16, int num_sms,
-                     cudaStream_t stream);
+constexpr int kProfStampBase = 16;
+constexpr int kProfStampCtas = 160;                       // >= CTAs per launch (148)
+constexpr int kProfWords = kProfStampBase + 4 * kProfStampCtas;
+int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p, int G, int is_fp16,
+                     int num_sms, cudaStream_t stream);
 int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident);
 void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int extra_bytes, int* stages, int* nbuf);
 #ifndef AY_EPI_PARTS

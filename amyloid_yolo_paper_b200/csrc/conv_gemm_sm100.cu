@@ -123,6 +123,14 @@ __device__ __forceinline__ void tma_load_pair(const CUtensorMap* map, uint32_t c
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(cluster_bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ unsigned long long global_timer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// PDL: block until every grid this launch depends on has completed and its writes are visible (no-op for a launch
+// without the programmatic-serialization attribute)
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -155,6 +163,17 @@ __device__ __forceinline__ void tmem_load32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// exp and reciprocal as single MUFU instructions (head decode fast path)
+__device__ __forceinline__ float fast_exp(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+  return r;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 template <bool FP16>
 __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
   if (FP16) {
@@ -170,11 +189,6 @@ __device__ __forceinline__ float2 unpack_pair(uint32_t w) {
   // bf16 -> fp32 is a 16-bit shift: two ALU ops per pair (the library conversion compiles to PRMT + two IMAD.U32)
   return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
 }
-__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
-
-// ---- epilogue staging: 32 rows x 32 channels (64-byte rows, TMA SWIZZLE_64B layout), nbuf (1|2) buffers per warp ----
-constexpr uint32_t kStageBufBytes = 32 * 64;
-constexpr int kMaxStageBufs = 2;
 __device__ __forceinline__ float2 add2(float2 a, float2 b) {
   unsigned long long r, x = *reinterpret_cast<unsigned long long*>(&a), y = *reinterpret_cast<unsigned long long*>(&b);
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(x), "l"(y));
@@ -192,27 +206,6 @@ constexpr int kBiasFloats = 1024;
 constexpr int kBK = 64;                 // channels per k-block: one 128-byte swizzle row
 constexpr uint32_t kRowBytes = 128;
 
-__device__ __forceinline__ void tma_load_local(const CUtensorMap* map, uint32_t bar, uint32_t dst, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
-               : "memory");
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-}
-__device__ __forceinline__ void tma_prefetch_l2(const CUtensorMap* map, int c0, int c1) {
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
-               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1)
-               : "memory");
-}
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
 // 256-bit global accesses (sm_100): a thread moves one whole 32-byte sector per instruction
 __device__ __forceinline__ void ldg256(const void* ptr, uint32_t* v) {
   asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -224,19 +217,11 @@ __device__ __forceinline__ void stg256(void* ptr, const uint32_t* v) {
                ::"l"(ptr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
                : "memory");
 }
-__device__ __forceinline__ void lds128(uint32_t addr, uint4& v) {
-  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
-}
-__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-
 // G = taps per pipeline stage (3: the kw taps of one kh share one 130-row A box; 1: one tap per stage)
 template <int G, bool FP16, bool SPLIT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes,
-                 const __grid_constant__ CUtensorMap tmResPF, const __grid_constant__ ConvGemmParams p) {
+                 const __grid_constant__ ConvGemmParams p) {
   // shared memory: [S pipeline stages][epilogue staging][mbarriers][tmem slot][bias]
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_addr(smem_raw) + 1023u) & ~1023u;
@@ -266,8 +251,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * S + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + kMaxAcc + a); };
-  auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * S + 2 * kMaxAcc + w * kMaxStageBufs + b); };
-  const uint32_t dummy_bar = bar_base + 8u * (2 * S + 2 * kMaxAcc + kEpiWarps * kMaxStageBufs);
+  const uint32_t dummy_bar = bar_base + 8u * (2 * S + 2 * kMaxAcc);
   const uint32_t bres_bar = dummy_bar + 8u;
   const uint32_t tmem_slot = bres_bar + 8u;
   // whole-layer bias staged once: with this much shared memory the L1 is ~1 KB, so a global bias load
@@ -276,6 +260,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // attribution stamps (profiling runs only): %globaltimer at entry / after the prologue / at exit of every CTA, and
+  // when the producer warp's wait for the previous layer returned
+  if (p.prof != nullptr && threadIdx.x == 0) p.prof[kProfStampBase + blockIdx.x] = global_timer();
   const uint32_t rank = blockIdx.x & 1u;            // == %cluster_ctarank for __cluster_dims__(2,1,1); warp-uniform
   const bool leader = rank == 0;
   // all 512 TMEM columns (one CTA per SM): 512/BN accumulators, so that the MMA issuer runs that many tiles ahead
@@ -287,8 +274,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmOut)) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmRes)) : "memory");
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < S; ++s) {
@@ -304,8 +289,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // leader's copy: the epilogue warps of both CTAs that work on a tile (all 8, or 4 when BN = 32: see `split`)
       bar_init(tempty_bar(a), tile_split ? 8 : 2 * kEpiWarps);   // arrivals per accumulator, both CTAs
     }
-    for (int w = 0; w < kEpiWarps; ++w)
-      for (int b = 0; b < kMaxStageBufs; ++b) bar_init(res_bar(w, b), 1);   // residual TMA loads, per epilogue warp
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -318,6 +301,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   fence_before();
   cluster_sync_all();
   fence_after();
+  // Programmatic dependent launch: everything above touched only constants (tensor maps, bias) and this CTA's own
+  // shared / tensor memory, so it ran while the previous layer's last CTAs were still finishing (this CTA became
+  // resident as soon as an SM was free).  Let the NEXT layer's CTAs do the same, then wait for the previous layer's
+  // results before the first dependent access (A loads, residual loads, every store).
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (p.prof != nullptr && threadIdx.x == 0) p.prof[kProfStampBase + kProfStampCtas + blockIdx.x] = global_timer();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
   if (tmem_base != 0u) {       // all 512 columns of an otherwise idle SM: the MMA warp relies on base 0 (uniform operand)
@@ -349,6 +338,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_load_pair(&tmB, lead_bres, smem_base + (uint32_t)t * b_tile, t * kBK, (int)rank * (p.BN / 2));
       }
       __syncwarp();
+      grid_dependency_wait();                     // (the resident weights above are constants: loaded before the wait)
+      if (p.prof != nullptr && lane == 0) p.prof[kProfStampBase + 3 * kProfStampCtas + blockIdx.x] = global_timer();
       for (int tile = first_tile; tile < total_tiles; tile += n_clusters) {
         const int m0 = (tile / p.num_n_tiles) * tile_rows + (int)rank * kRowsPerCta * R;   // this CTA's rows are contiguous
         const int n0 = (tile % p.num_n_tiles) * p.BN + (int)rank * (p.BN / 2);
@@ -487,6 +478,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else {
     // ---------------- epilogue: warps 2..9; TMEM lane quarter = warp % 4, chunk parity = (warp-2)/4 ----------------
+    grid_dependency_wait();
     const int ew = warp - 2;
     const int quarter = warp & 3;
     const int part = ew >> 2;
@@ -694,6 +686,35 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const bool one_image = __all_sync(0xffffffffu, !valid || img == img_first) != 0;
         const bool staged = p.head_stage_bytes > 0 && one_image;
         float* hs = reinterpret_cast<float*>(smem_raw + (staging_base - smem_addr(smem_raw)) + (uint32_t)ew * (uint32_t)p.head_stage_bytes);
+        if (p.head_fast) {
+          // The shipped detector's head: 3 anchors x (5 + 2 classes) = 21 channels in ONE 32-column chunk.  Anchor and
+          // field of every channel are compile-time constants here (no select chain per channel), and the two
+          // transcendentals are single MUFU instructions: ex2.approx on t*log2(e) and rcp.approx, each within 2 ulp -
+          // four orders of magnitude below the 16-bit activations' own error on these outputs (the generic path below
+          // and the stand-alone decode_kernel keep expf and the IEEE division).
+          uint32_t v[32];
+          tmem_load32(t_acc, v);
+          const float fgx = (float)gx, fgy = (float)gy;
+#pragma unroll
+          for (int a = 0; a < 3; ++a) {
+            float r[7];
+#pragma unroll
+            for (int f = 0; f < 7; ++f) {
+              const float t = __uint_as_float(v[a * 7 + f]) + s_bias[a * 7 + f];
+              if (f == 2 || f == 3) {
+                r[f] = __fmul_rn(__fmul_rn(fast_exp(t), f == 2 ? p.anchor_w[a] : p.anchor_h[a]), p.stride);
+              } else {
+                const float sg = fast_rcp(1.0f + fast_exp(-t));
+                r[f] = f < 2 ? __fmul_rn(__fadd_rn(sg, f == 0 ? fgx : fgy), p.stride) : sg;
+              }
+            }
+            if (valid && !(p.dbg & 256)) {
+              float* dst = staged ? hs + (a * 32 + rank_v) * 7 : obase + (size_t)a * a_step;
+#pragma unroll
+              for (int f = 0; f < 7; ++f) dst[f] = r[f];
+            }
+          }
+        } else
         for (int c = c_first; c < nchunks; c += c_step) {
           uint32_t v[32];
           tmem_load32(t_acc + (uint32_t)(c * 32), v);
@@ -761,6 +782,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
+  if (p.prof != nullptr && threadIdx.x == 0) p.prof[kProfStampBase + 2 * kProfStampCtas + blockIdx.x] = global_timer();
 }
 
 }  // namespace
@@ -772,7 +794,7 @@ int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident) {
 
 static int conv_gemm_fixed_smem(int num_stages, int nbuf, int extra_bytes = 0) {
   (void)nbuf;
-  return extra_bytes + 8 * (2 * num_stages + 2 * kMaxAcc + kEpiWarps * kMaxStageBufs + 2) + 32 +
+  return extra_bytes + 8 * (2 * num_stages + 2 * kMaxAcc + 2) + 32 +
          4 * kBiasFloats + 1024 /*alignment*/;
 }
 
@@ -795,9 +817,8 @@ static void magic_div(unsigned d, int nbits, unsigned* mul, int* shift) {
   *mul = (unsigned)(((1ull << *shift) + d - 1) / d);
 }
 
-int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmRes,
-                     const CUtensorMap& tmResPF, const ConvGemmParams& p_in, int G, int is_fp16, int num_sms,
-                     cudaStream_t stream) {
+int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p_in, int G, int is_fp16,
+                     int num_sms, cudaStream_t stream) {
   ConvGemmParams p = p_in;
   {
     // rows reach P rounded up to whole tiles (plus the row batch of the last one)
@@ -840,10 +861,23 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
     p.epi_dr = t_step - dq * p.num_n_tiles;
     p.epi_qrows = dq * 256 * p.m_batch;
   }
+  // Programmatic dependent launch (chained layers): this grid's CTAs may become resident, and run their prologue,
+  // while the previous kernel in the stream drains; the kernel itself waits (griddepcontrol.wait) before touching
+  // anything the previous kernel wrote.
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kThreads2);
+  cfg.dynamicSmemBytes = (size_t)smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.pdl ? 1 : 0;
 #define AY_LAUNCH3(GG, FF, SS)                                                                                             \
   do {                                                                                                                     \
     AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<GG, FF, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));  \
-    conv_gemm_kernel<GG, FF, SS><<<grid, kThreads2, smem, stream>>>(tmA, tmB, tmOut, tmRes, tmResPF, p);                   \
+    AY_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<GG, FF, SS>, tmA, tmB, p));                                          \
   } while (0)
 #define AY_LAUNCH(GG, FF) do { if (split) AY_LAUNCH3(GG, FF, true); else AY_LAUNCH3(GG, FF, false); } while (0)
   if (G == 3) { if (is_fp16) AY_LAUNCH(3, true); else AY_LAUNCH(3, false); }

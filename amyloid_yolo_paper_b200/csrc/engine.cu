@@ -132,9 +132,8 @@ struct Layer {
   bool fused_into_producer = false; // upsample: written by the producing conv
   int plane_mode = 0;               // conv: 1 = rows and planes, 2 = planes only (nothing else reads the rows)
   float* raw_f32 = nullptr;         // reference path scratch for heads
-  // tmA: a_rows x 64-channel box of the input (or parity planes); tmB: BN/2 x 64 box of the weights;
-  // tmOut/tmRes: 32-row x 32-channel boxes of the epilogue's TMA store / residual load; tmResPF: L2 prefetch box
-  CUtensorMap tmA, tmB, tmOut, tmRes, tmResPF;
+  // tmA: a_rows x 64-channel box of the input (or parity planes); tmB: BN/2 x 64 box of the weights
+  CUtensorMap tmA, tmB;
   // yolo
   int dec_row_off = 0;
   // route copy fallback
@@ -160,6 +159,8 @@ struct ay_ctx {
   bool is_f32 = false;                // AY_F32 network: every block runs the fp32 kernels of fp32_path.cu
   float* f_in = nullptr;              // AY_F32: staged input [B,S+2,S+2,3]
   int dbg = 0;                        // AY_DBG ablation bits (see ConvGemmParams::dbg)
+  bool no_head_fast = false;          // AY_NO_HEADFAST=1: generic decode epilogue for every head
+  bool pdl = true;                    // chain the convolution launches with programmatic dependent launch (AY_NO_PDL=1: off)
   int dec_rows = 0, dec_cols = 0;
   int* idx_y = nullptr;               // nearest-resize tables (device), rebuilt when the source size changes
   int* idx_x = nullptr;
@@ -168,6 +169,7 @@ struct ay_ctx {
   int launches = 0;
   // per-layer timing (ay_forward_profile): one event before every cfg block and one after the last
   bool profiling = false;
+  bool stamping = false;              // ay_forward_stamps: per-CTA %globaltimer stamps, no events between the launches
   std::vector<cudaEvent_t> prof_events;
   unsigned long long* prof_counters = nullptr;   // [n_layers][16], device
   // post-processing scratch
@@ -268,6 +270,8 @@ extern "C" int ay_create(ay_ctx** out, int device) {
   }
   cudaMemset(ctx->err_flag, 0, sizeof(unsigned int));
   if (const char* e = getenv("AY_DBG")) ctx->dbg = atoi(e);
+  if (getenv("AY_NO_PDL")) ctx->pdl = false;
+  if (getenv("AY_NO_HEADFAST")) ctx->no_head_fast = true;
   *out = ctx;
   return AY_OK;
 }
@@ -295,6 +299,11 @@ extern "C" int ay_check(ay_ctx* ctx, void* stream) {
   if (flag) {
     AY_CUDA(cudaMemset(ctx->err_flag, 0, sizeof(flag)));
     if ((flag & 0xFFFF0000u) == 0xCA9A0000u) {
+      if ((flag & 0xFFFF) == 4) {
+        set_error("merge: a detection holds a non-finite value (the reference raises OverflowError/ValueError at int(), "
+                  "core.py:330-337)");
+        return AY_EINVAL;
+      }
       set_error("per-tile capacity exceeded in %s", (flag & 0xFFFF) == 1 ? "nms (more kept boxes than cap)"
                                                     : (flag & 0xFFFF) == 2 ? "merge (more than 512 detections in a tile)"
                                                                            : "merge (entry pool)");
@@ -635,17 +644,6 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     } else {
       AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, 64, L.a_rows, ctx->is_fp16));
     }
-    if (!L.is_head) {
-      const ActView& tgt = L.fused_shortcut >= 0 ? Ls[L.fused_shortcut].out : L.out;
-      AY_TRY(ay::make_map_2d(&L.tmOut, tgt.ptr, tgt.Cp, tgt.rows_alloc, tgt.pitch, 32, 32, ctx->is_fp16));
-      const ActView& rv = L.residual_src >= 0 ? Ls[L.residual_src].out : tgt;
-      AY_TRY(ay::make_map_2d(&L.tmRes, rv.ptr, rv.Cp, rv.rows_alloc, rv.pitch, 32, 32, ctx->is_fp16));
-      AY_TRY(ay::make_map_2d(&L.tmResPF, rv.ptr, rv.Cp, rv.rows_alloc, rv.pitch, L.BN, 128, ctx->is_fp16, /*swizzle=*/false));
-    } else {
-      L.tmOut = L.tmA;
-      L.tmRes = L.tmA;
-      L.tmResPF = L.tmA;
-    }
     if (L.is_head)
       AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.raw_f32),
                            sizeof(float) * (size_t)ay::padded_rows(max_batch, L.H, L.W) * L.cout_rows, true));
@@ -952,10 +950,13 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   q.Hp = Hq; q.Wp = Wq;
   q.bias = L.bias; q.leaky = L.d.leaky;
   q.err_flag = ctx->err_flag;
-  q.prof = (ctx->profiling && ctx->prof_counters) ? ctx->prof_counters + (size_t)i * 16 : nullptr;
+  q.prof = ((ctx->profiling || ctx->stamping) && ctx->prof_counters) ? ctx->prof_counters + (size_t)i * ay::kProfWords : nullptr;
+  q.pdl = ctx->pdl ? 1 : 0;
   if (L.is_head) {
     q.head = 1;
     q.head_stage_bytes = L.head_stage_bytes;
+    q.head_fast = (ctx->dec_cols == 7 && Y->d.n_anchors == 3 && L.C == 21 && L.BN == 32 && L.cout_rows == 32 &&
+                   L.m_batch == 1 && !ctx->no_head_fast) ? 1 : 0;
     q.dec_out = dec_out; q.dec_rows_total = ctx->dec_rows; q.dec_row_off = Y->dec_row_off;
     q.dec_cols = ctx->dec_cols; q.n_anchors = Y->d.n_anchors; q.cout = L.C;
     const double stride = (double)ctx->img_size / (double)L.H;   // models.py:119
@@ -984,7 +985,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
     }
   }
   ++ctx->launches;
-  return ay::launch_conv_gemm(L.tmA, L.tmB, L.tmOut, L.tmRes, L.tmResPF, q, L.G, ctx->is_fp16, ctx->num_sms, st);
+  return ay::launch_conv_gemm(L.tmA, L.tmB, q, L.G, ctx->is_fp16, ctx->num_sms, st);
 }
 
 }  // namespace
@@ -1086,9 +1087,9 @@ extern "C" int ay_forward_profile(ay_ctx* ctx, const void* input, int in_kind, i
     AY_CUDA(cudaEventCreate(&e));
     ctx->prof_events.push_back(e);
   }
-  if (!ctx->prof_counters) AY_CUDA(cudaMalloc(&ctx->prof_counters, sizeof(unsigned long long) * 16 * ctx->layers.size()));
-  AY_CUDA(cudaMemsetAsync(ctx->prof_counters, 0, sizeof(unsigned long long) * 16 * ctx->layers.size(),
-                          static_cast<cudaStream_t>(stream)));
+  const size_t prof_bytes = sizeof(unsigned long long) * ay::kProfWords * ctx->layers.size();
+  if (!ctx->prof_counters) AY_CUDA(cudaMalloc(&ctx->prof_counters, prof_bytes));
+  AY_CUDA(cudaMemsetAsync(ctx->prof_counters, 0, prof_bytes, static_cast<cudaStream_t>(stream)));
   ctx->profiling = true;
   const int rc = ay_forward(ctx, input, in_kind, batch, src_h, src_w, out_decoded, stream);
   ctx->profiling = false;
@@ -1099,13 +1100,36 @@ extern "C" int ay_forward_profile(ay_ctx* ctx, const void* input, int in_kind, i
   return AY_OK;
 }
 
+extern "C" int ay_prof_words(void) { return ay::kProfWords; }
+
+extern "C" int ay_forward_stamps(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                                 float* out_decoded, void* stream, unsigned long long* stamps_h, int n_layers) {
+  AY_ENTER(ctx);
+  if (!stamps_h || n_layers != (int)ctx->layers.size()) {
+    set_error("ay_forward_stamps: expected %d layer slots", (int)ctx->layers.size());
+    return AY_EINVAL;
+  }
+  const size_t prof_bytes = sizeof(unsigned long long) * ay::kProfWords * ctx->layers.size();
+  if (!ctx->prof_counters) AY_CUDA(cudaMalloc(&ctx->prof_counters, prof_bytes));
+  AY_CUDA(cudaMemsetAsync(ctx->prof_counters, 0, prof_bytes, static_cast<cudaStream_t>(stream)));
+  ctx->stamping = true;
+  const int rc = ay_forward(ctx, input, in_kind, batch, src_h, src_w, out_decoded, stream);
+  ctx->stamping = false;
+  if (rc != AY_OK) return rc;
+  AY_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  AY_CUDA(cudaMemcpy(stamps_h, ctx->prof_counters, prof_bytes, cudaMemcpyDeviceToHost));
+  return AY_OK;
+}
+
 extern "C" int ay_debug_counters(ay_ctx* ctx, unsigned long long* out_h, int n_layers) {
   AY_ENTER(ctx);
   if (!out_h || n_layers != (int)ctx->layers.size() || !ctx->prof_counters) {
     set_error("ay_debug_counters: call ay_forward_profile first");
     return AY_ESTATE;
   }
-  AY_CUDA(cudaMemcpy(out_h, ctx->prof_counters, sizeof(unsigned long long) * 16 * n_layers, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < n_layers; ++i)
+    AY_CUDA(cudaMemcpy(out_h + (size_t)i * 16, ctx->prof_counters + (size_t)i * ay::kProfWords, sizeof(unsigned long long) * 16,
+                       cudaMemcpyDeviceToHost));
   return AY_OK;
 }
 

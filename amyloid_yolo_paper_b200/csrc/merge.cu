@@ -236,6 +236,7 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
   PySet live;
   live.init(ts);
   // rescale + tuple hash of the n detections: independent, one lane each (the FP64 hash is most of a small tile's time)
+  bool finite = true;
   for (int r = lane; r < n; r += 32) {
     Entry& e = ts->pool[r];
     e.v[0] = (double)__fmul_rn(__fdiv_rn(__fsub_rn(in[r * 7 + 0], pad_x_half), unpad_w), orig_w);
@@ -245,8 +246,19 @@ __global__ void rescale_merge_kernel(const float* __restrict__ rows, const int32
     e.v[4] = (double)in[r * 7 + 4];
     e.v[5] = (double)in[r * 7 + 5];
     e.v[6] = (double)in[r * 7 + 6];
-    e.hash = hash_tuple7(e.v);
+    // A non-finite field (exp overflow in the decode, an inf activation) has no tuple hash here: frexp(inf) = inf and
+    // NaN != 0 forever, so hash_double would never return.  The reference fails loudly as well (int(inf) raises
+    // OverflowError, int(nan) ValueError in combineIfOverlapping, core.py:330-337): report it instead of hanging.
+    bool ok = true;
+    for (int c = 0; c < 7; ++c) ok = ok && isfinite(e.v[c]);
+    if (ok) e.hash = hash_tuple7(e.v);
+    else finite = false;
     ts->gflag[r] = 0;
+  }
+  finite = __all_sync(0xffffffffu, finite);
+  if (!finite) {
+    if (lane == 0) { atomicExch(err_flag, 0xCA9A0004u); out_counts[b] = -1; }
+    return;
   }
   __syncwarp();
   if (lane != 0) return;              // the fixed point itself is serial (set iteration order)

@@ -388,11 +388,8 @@ int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thr
   int np2 = 1;
   while (np2 < n_rows) np2 <<= 1;
   const size_t sort_smem = sizeof(unsigned long long) * (size_t)np2;
-  static size_t configured = 0;
-  if (sort_smem > configured) {
-    AY_CUDA(cudaFuncSetAttribute(nms_prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    configured = 160 * 1024;
-  }
+  // per launch, like conv_gemm: the attribute is per DEVICE (a process may drive several GPUs) and setting it is cheap
+  AY_CUDA(cudaFuncSetAttribute(nms_prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
   uint8_t* sc = static_cast<uint8_t*>(scratch);
   nms_prepare_kernel<<<batch, kSortThreads, sort_smem, s>>>(pred, n_rows, n_classes, conf_thres, sc, L);
   AY_CUDA(cudaGetLastError());

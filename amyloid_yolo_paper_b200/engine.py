@@ -87,7 +87,7 @@ def fold_batchnorm(module_defs, state, layer):
 
 
 class Engine:
-    def __init__(self, module_defs, hyperparams, state_dict, device, max_batch=8, precision="bf16"):
+    def __init__(self, module_defs, hyperparams, state_dict, device, max_batch=8, precision="bf16", img_size=None):
         if not torch.cuda.is_available():
             raise _lib.EngineUnavailable("no CUDA device: the B200 engine has no CPU fallback")
         self.device = torch.device(device)
@@ -99,7 +99,11 @@ class Engine:
         self.module_defs = module_defs
         self.max_batch = int(max_batch)
         self.precision = precision
-        self.img_size = int(hyperparams["height"])
+        # network input size: the cfg's [net] height unless the caller runs the network at another
+        # multiple of 32 (the reference takes img_dim from the input tensor, models.py:238)
+        self.img_size = int(img_size) if img_size is not None else int(hyperparams["height"])
+        if self.img_size < 32 or self.img_size % 32 != 0:
+            raise ValueError("network input size must be a positive multiple of 32 (got %d)" % self.img_size)
         self.in_channels = int(hyperparams["channels"])
         self.ctx = ctypes.c_void_p()
         code = self.lib.ay_create(ctypes.byref(self.ctx), self.index)

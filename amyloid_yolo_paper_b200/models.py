@@ -109,36 +109,79 @@ class Darknet(nn.Module):
         self._engine = None           # built lazily on first forward (needs a GPU)
         self._engine_key = None
         self._weights_epoch = 0
+        self._tensor_cache = None
         # "bf16" | "fp16": activation storage of the tensor-core path (2e-2 bar on the raw heads);
         # "fp32": the accuracy mode, fp32 storage + FFMA accumulation on the CUDA cores (1e-4 bar)
         self.precision = "bf16"
 
     # ------------------------------------------------------------------ engine
-    def engine(self, device=None, max_batch=None):
-        """The sm_100a execution engine for this network (created on demand and
-        re-created when the weights, device or batch capacity change)."""
+    def invalidate_engine(self):
+        """Force the next forward to re-fold and re-upload the weights.  Needed only after writes the
+        staleness key cannot see: ``param.data.copy_()/fill_()`` (``.data`` has its own version counter)."""
+        self._weights_epoch += 1
+
+    def _staleness_key(self):
+        """Cheap per-call key: the tensors are listed once (no ``state_dict()`` walk per forward, which was
+        first-order at batch 1) and only their identity and in-place version counters are read."""
+        cache = self._tensor_cache
+        if cache is None:
+            cache = self._tensor_cache = tuple(self.parameters()) + tuple(self.buffers())
+        v = 0
+        for t in cache:
+            v += t._version
+        return (self._weights_epoch, v, cache[0].data_ptr() if cache else 0)
+
+    def _apply(self, fn, *args, **kwargs):
+        # .to() / .cuda() / .float(): parameters are re-created
+        self._tensor_cache = None
+        self._weights_epoch += 1
+        return super()._apply(fn, *args, **kwargs)
+
+    def apply(self, fn):
+        # model.apply(weights_init_normal) writes through .data (utils/utils.py:27-33)
+        out = super().apply(fn)
+        self._tensor_cache = None
+        self._weights_epoch += 1
+        return out
+
+    def load_state_dict(self, *args, **kwargs):
+        out = super().load_state_dict(*args, **kwargs)
+        self._tensor_cache = None
+        self._weights_epoch += 1
+        return out
+
+    def engine(self, device=None, max_batch=None, img_size=None):
+        """The sm_100a execution engine for this network (created on demand and re-created when the
+        weights, device, precision, input size or batch capacity change).  A replaced engine is not
+        destroyed here: it is released when its last user (e.g. a :class:`TileDetector`) lets go of it,
+        so nobody is left holding a freed ``ay_ctx``."""
         from .engine import Engine
         if device is None:
             p = next(self.parameters())
             device = p.device if p.is_cuda else torch.device("cuda", torch.cuda.current_device()
                                                              if torch.cuda.is_available() else 0)
-        version = tuple(int(p._version) for p in self.state_dict().values())
-        key = (str(device), version, self.precision, self._weights_epoch)
-        if self._engine is None or self._engine_key != key or \
-                (max_batch is not None and max_batch > self._engine.max_batch):
-            if self._engine is not None:
-                self._engine.close()
+        device = torch.device(device)
+        size = int(img_size) if img_size is not None else int(self.hyperparams["height"])
+        key = (device.type, device.index, self.precision, size, self._staleness_key())
+        eng = self._engine
+        if eng is None or self._engine_key != key or (max_batch is not None and max_batch > eng.max_batch):
+            cap = max(int(max_batch or 8), eng.max_batch if (eng is not None and self._engine_key == key) else 0)
+            self._engine = None           # drop our reference first: frees the old buffers unless someone else holds it
+            del eng
             self._engine = Engine(self.module_defs, self.hyperparams, self.state_dict(), device,
-                                  max_batch=max_batch or 8, precision=self.precision)
+                                  max_batch=cap, precision=self.precision, img_size=size)
             self._engine_key = key
         return self._engine
 
     def forward(self, x, targets=None):
         """x: [B,3,S,S] float (S multiple of 32) -> CPU fp32 [B, sum(A*G*G), 5+C]
-        (reference ``models.py:237-255``)."""
+        (reference ``models.py:237-255``; like the reference the network runs at the input's own size,
+        ``img_dim = x.shape[2]``, models.py:238)."""
         if targets is not None:
             raise NotImplementedError("training branch (models.py:173-222) is out of scope")
-        eng = self.engine(max_batch=x.shape[0])
+        if x.dim() != 4 or x.shape[2] != x.shape[3] or x.shape[2] % 32 != 0:
+            raise ValueError("expected input [B,C,S,S] with S a multiple of 32, got %s" % (tuple(x.shape),))
+        eng = self.engine(max_batch=x.shape[0], img_size=x.shape[2])
         out = eng.forward_nchw(x)
         eng.check()
         return out.cpu()

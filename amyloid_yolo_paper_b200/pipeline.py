@@ -35,7 +35,7 @@ class TileDetector:
     """
 
     def __init__(self, model, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=64, cap=256,
-                 device=None):
+                 device=None, img_size=None):
         if not torch.cuda.is_available():
             raise _lib.EngineUnavailable("no CUDA device: the B200 pipeline has no CPU fallback")
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
@@ -46,12 +46,13 @@ class TileDetector:
         self.nms_thres = float(nms_thres)
         self.merge_boxes = bool(merge_boxes)
         self.max_batch = int(max_batch)
-        self.engine = model.engine(device=self.device, max_batch=self.max_batch)
-        self.img_size = self.engine.img_size
-        self.rows, self.cols = self.engine.rows, self.engine.cols
+        # network input size: what detect.py passes as --img_size to Darknet(...) and to Resize/rescale_boxes
+        # (detect.py:59,73,129); the engine is planned for that size, any multiple of 32
+        self.img_size = int(img_size if img_size is not None else getattr(model, "img_size", 0) or
+                            model.hyperparams["height"])
+        self.engine = None
+        self._bind_engine()
         self.cap = int(min(cap, self.rows))
-        self.lib = self.engine.lib
-        self.ctx = self.engine.ctx          # NMS / merge scratch lives in the same context as the network
         B, dev = self.max_batch, self.device
         self.decoded = torch.empty((B, self.rows, self.cols), dtype=torch.float32, device=dev)
         self.nms_rows = torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev)
@@ -65,6 +66,24 @@ class TileDetector:
 
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _bind_engine(self):
+        """(Re)fetch the model's engine.  ``Darknet.engine()`` replaces its engine when the weights, the
+        precision or the batch capacity change; this detector keeps a reference to the engine object it
+        runs on (never a bare ``ay_ctx`` pointer), so a replaced engine stays alive until this call has
+        switched over and nothing ever runs on a destroyed context."""
+        eng = self.model.engine(device=self.device, max_batch=self.max_batch, img_size=self.img_size)
+        if eng is not self.engine:
+            if self.engine is not None and (eng.rows, eng.cols) != (self.rows, self.cols):
+                raise RuntimeError("the model's output shape changed under a live TileDetector")
+            self.engine = eng
+            self.rows, self.cols = eng.rows, eng.cols
+            self.lib = eng.lib
+        return eng
+
+    @property
+    def ctx(self):
+        return self.engine.ctx              # NMS / merge scratch lives in the same context as the network
 
     # ------------------------------------------------------------------ device side
     def run_device(self, tiles, original_shape=None, slot=0):
@@ -87,6 +106,7 @@ class TileDetector:
         if original_shape is None:
             original_shape = (sh, sw)
         st = self._stream()
+        self._bind_engine()
         lib, ctx = self.lib, self.ctx
         with torch.cuda.device(self.device):
             _lib.check(lib.ay_forward(ctx, _ptr(tiles), kind, B, sh, sw, _ptr(self.decoded), st))

@@ -166,3 +166,137 @@ def synthetic_detections(count, seed=0, extent=1536.0, num_classes=2, overlap=0.
         rows[i] = (cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2,
                    rng.uniform(0.8, 1.0), rng.uniform(0.5, 1.0), cls)
     return rows
+
+
+# ----------------------------------------------------------------------------- planted objects
+# A seeded random checkpoint has a Gaussian objectness tail: every row that clears conf_thres sits within the 16-bit
+# activations' noise of the threshold, so "final detections agree" cannot be tested on it in bf16.  A trained detector
+# is bimodal instead (object / no object).  The checkpoint below gets that property by construction: three MARKER
+# channels carry a sub-sampled copy of the input's R, G and B planes through the whole network unchanged (centre-tap
+# unit weights, identity BatchNorm, zero contribution from the residual branches), and the objectness / class logits of
+# head h (grid 13, 26, 52) read marker h only.  Setting one source pixel of a tile plants one confident detection at a
+# chosen grid cell; every other pixel and every other channel stays random, so the box regressions of the planted rows
+# still come through all 75 random convolutions.
+PLANT_CONF_GAIN, PLANT_CONF_BIAS = 8.0, -2.5     # t_conf = 8 m - 2.5: m = 0 -> conf 0.076; m in [0.58, 1] -> 0.90 .. 0.996
+PLANT_CLS_GAIN, PLANT_CLS_MID = 30.0, 0.794      # class 0 for m > 0.794 (pixel value > 202), class 1 below
+PLANT_VALUES = {0: (215, 255), 1: (150, 190)}    # marker pixel values per class (distinct per object: distinct scores)
+
+
+def planted_state_dict(model, seed=0, anchor=(0, 2, 2), xy_gain=0.3, wh_gain=0.05):
+    """Seeded random checkpoint of ``model`` (yolov3-custom layout: no maxpool) with the marker channels described above.
+    Head h fires on anchor ``anchor[h]`` only.  Returns the state_dict (also loaded into ``model``)."""
+    sd = synthetic_state_dict(model, seed=seed, conf_bias=None, wh_gain=None)
+    defs = model.module_defs
+    marks = []                     # per layer: input-channel index of the three markers in that layer's OUTPUT (or None)
+    cur = [0, 1, 2]                # the network input itself: R, G, B
+    channels = [int(model.hyperparams["channels"])]
+    head = 0
+    for i, d in enumerate(defs):
+        t = d["type"]
+        pre = "module_list.%d." % i
+        if t == "convolutional":
+            w = sd[pre + "conv_%d.weight" % i]
+            k = w.shape[2]
+            is_head = i + 1 < len(defs) and defs[i + 1]["type"] == "yolo"
+            if is_head:
+                per = w.shape[0] // 3
+                classes = per - 5
+                if classes != 2:
+                    raise ValueError("planted checkpoint is defined for 2 classes")
+                for a in range(3):
+                    base = a * per
+                    w[base:base + 2] *= xy_gain
+                    w[base + 2:base + 4] *= wh_gain
+                    sd[pre + "conv_%d.bias" % i][base:base + 4] *= xy_gain
+                    w[base + 4:base + per] = 0.0
+                    b = sd[pre + "conv_%d.bias" % i]
+                    if a == anchor[min(head, len(anchor) - 1)] and cur is not None:
+                        m = cur[min(head, 2)]
+                        w[base + 4, m, 0, 0] = PLANT_CONF_GAIN
+                        b[base + 4] = PLANT_CONF_BIAS
+                        w[base + 5, m, 0, 0] = PLANT_CLS_GAIN
+                        b[base + 5] = -PLANT_CLS_GAIN * PLANT_CLS_MID
+                        w[base + 6, m, 0, 0] = -PLANT_CLS_GAIN
+                        b[base + 6] = PLANT_CLS_GAIN * PLANT_CLS_MID
+                    else:
+                        b[base + 4] = -8.0
+                        b[base + 5:base + per] = 0.0
+                head += 1
+                nxt = None
+            else:
+                ends_branch = i + 1 < len(defs) and defs[i + 1]["type"] == "shortcut"
+                for j in range(3):
+                    w[j] = 0.0
+                    if not ends_branch and cur is not None:
+                        w[j, cur[j], k // 2, k // 2] = 1.0          # centre tap: out(y,x) = in(s*y, s*x)
+                    bn = pre + "batch_norm_%d." % i
+                    sd[bn + "weight"][j] = 1.0
+                    sd[bn + "bias"][j] = 0.0
+                    sd[bn + "running_mean"][j] = 0.0
+                    sd[bn + "running_var"][j] = 1.0 - 1e-5          # gamma / sqrt(var + eps) = 1
+                nxt = None if ends_branch else [0, 1, 2]
+            channels.append(w.shape[0])
+        elif t == "shortcut":
+            nxt = marks[i + int(d["from"])]                           # branch contributes exactly 0 on the marker channels
+            channels.append(channels[-1])
+        elif t == "route":
+            srcs = [int(v) for v in d["layers"].split(",")]
+            srcs = [s if s >= 0 else i + s for s in srcs]
+            off, nxt = 0, None
+            for s in srcs:                                            # the last source that carries markers wins (the
+                if marks[s] is not None:                              # non-upsampled one of [upsample, stage output])
+                    nxt = [off + c for c in marks[s]]
+                off += channels[s + 1]
+            channels.append(off)
+        elif t == "upsample":
+            nxt = cur
+            channels.append(channels[-1])
+        elif t == "yolo":
+            nxt = None
+            channels.append(channels[-1])
+        else:
+            raise ValueError("planted checkpoint: unsupported block [%s]" % t)
+        marks.append(nxt)
+        cur = nxt
+    model.load_state_dict(sd)
+    return model.state_dict()
+
+
+def planted_tiles(batch, size=1536, seed=7, img=416, objects=(10, 16), grids=(13, 26), pair_share=0.35):
+    """uint8 [batch,size,size,3] random tiles with planted objects for :func:`planted_state_dict`.
+    -> (tiles, truth) where truth[b] is a list of (grid, gy, gx, class, value).  Marker h (R, G, B for grids
+    13, 26, 52) is sampled at network pixel (stride*gy, stride*gx), i.e. source pixel floor(p*size/img) under the
+    nearest resize: those source pixels are zeroed everywhere and set to a distinct value per planted object.
+    ``pair_share`` of the objects get a same-class neighbour in the adjacent cell (an IoU > 0.4 cluster for NMS,
+    overlapping boxes for mergeDetections)."""
+    rng = np.random.default_rng([seed, batch, size])
+    tiles = rng.integers(0, 256, size=(batch, size, size, 3), dtype=np.uint8)
+    scale = np.float32(size) / np.float32(img)
+    src = np.minimum(np.floor(np.arange(img, dtype=np.float32) * scale).astype(np.int64), size - 1)
+    all_grids = (13, 26, 52)
+    truth = []
+    for b in range(batch):
+        for h, g in enumerate(all_grids):                 # background: marker planes read 0 at every sampled position
+            pos = src[np.arange(g) * (img // g)]
+            tiles[b][np.ix_(pos, pos, [h])] = 0
+        used, objs = set(), []
+        values = {c: list(rng.permutation(np.arange(lo, hi + 1))) for c, (lo, hi) in PLANT_VALUES.items()}
+        n = int(rng.integers(objects[0], objects[1] + 1))
+        while len(objs) < n:
+            g = int(rng.choice(grids))
+            gy, gx = (int(v) for v in rng.integers(1, g - 2, 2))
+            cls = int(rng.integers(0, 2))
+            cells = [(gy, gx)]
+            if rng.random() < pair_share:
+                cells.append((gy, gx + 1))
+            if any((g, y + dy, x + dx) in used for y, x in cells for dy in (-1, 0, 1) for dx in (-1, 0, 1)):
+                continue
+            for y, x in cells:
+                used.add((g, y, x))
+                objs.append((g, y, x, cls, int(values[cls].pop())))
+        for g, gy, gx, cls, val in objs:
+            h = all_grids.index(g)
+            stride = img // g
+            tiles[b, src[stride * gy], src[stride * gx], h] = val
+        truth.append(objs)
+    return tiles, truth

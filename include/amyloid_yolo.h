@@ -128,6 +128,14 @@ int  ay_forward_profile(ay_ctx* ctx, const void* input, int in_kind, int batch, 
 int  ay_debug_set(ay_ctx* ctx, int bits);
 /* Cycle counters of the last ay_forward_profile: 16 per layer (meaning: conv_gemm_sm100.cu). */
 int  ay_debug_counters(ay_ctx* ctx, unsigned long long* out_h, int n_layers);
+/* Attribution of one forward WITHOUT events between the launches (so launch gaps and the overlap of chained
+ * launches are what a normal ay_forward sees): every convolution CTA stamps %globaltimer (ns) at entry, at the
+ * end of its prologue and at exit.  stamps_h: [n_layers][ay_prof_words()] — words 0..15 as ay_debug_counters,
+ * then 4 blocks of 160 words (entry / prologue end / exit / wait for the previous layer returned, indexed by
+ * CTA; 0 = CTA not launched).  Synchronises. */
+int  ay_prof_words(void);
+int  ay_forward_stamps(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                       float* out_decoded, void* stream, unsigned long long* stamps_h, int n_layers);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,282 @@
+"""GPU parity tests, part 2 (``-m gpu``): the north_star bars that round 1 left unasserted, and the benched sizes.
+
+* final detections >= 99.5 % matched at IoU >= 0.99 against the all-fp32 oracle chain — asserted in bf16 on a
+  checkpoint with bimodal objectness (``synth.planted_state_dict``) and in the fp32 mode on the Gaussian one;
+* BASELINE.json's batch sizes: custom cfg at B = 256, tiny cfg at B = 64, NMS at B = 128 x 10 647 rows;
+* regressions for the round-1 advisor findings (engine lifetime under a live TileDetector, --img_size,
+  non-finite rows in mergeDetections, several contexts in one process).
+Everything goes through the C ABI (ctypes); nothing here reads /root/reference.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import raw_head_error
+from oracle import restate as R
+from test_gpu_parity import _match_rate, _model, bits
+
+pytestmark = pytest.mark.gpu
+
+MATCH_BAR = 0.995        # north_star: final detections agree with at least 99.5 % matched at IoU >= 0.99
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda", 0)
+
+
+def _oracle_final(dec, size=416, orig=(1536, 1536)):
+    rows, _ = R.nms_exact(dec, 0.8, 0.4)
+    if rows is None:
+        return np.zeros((0, 7), np.float32)
+    return R.merge_emulated(R.rescale_boxes(rows.copy(), size, orig))
+
+
+def _two_way_rate(got, want):
+    total = matched = 0
+    for g, w in zip(got, want):
+        g = np.zeros((0, 7), np.float32) if g is None else (g.numpy() if isinstance(g, torch.Tensor) else g)
+        total += len(g) + len(w)
+        matched += _match_rate(w, g) * len(w) + _match_rate(g, w) * len(g)
+    return matched / max(total, 1), total
+
+
+# ------------------------------------------------------------------ the 99.5 % bar
+def test_final_detections_bar_bf16_planted_checkpoint(dev):
+    """bf16 tensor-core path, checkpoint with bimodal objectness: every planted object is a confident candidate in both
+    evaluations, the box regressions of those rows come through all 75 (random) convolutions in 16-bit storage, and
+    the final detections (NMS clusters, rescale, integer hulls of mergeDetections) must match the all-fp32 oracle."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.models import Darknet
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    cfg = ensure_cfg("yolov3-custom")
+    m = Darknet(cfg)
+    sd = synth.planted_state_dict(m, seed=1)
+    blocks = R.parse_cfg(cfg)
+    B = 8
+    tiles, truth = synth.planted_tiles(B, seed=9)
+    det = TileDetector(m, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=B, cap=512, device=dev)
+    got = det.detect(torch.from_numpy(tiles))
+    dec_gpu = det.engine.forward_u8(torch.from_numpy(tiles)).cpu().numpy()
+    det.check()
+    x = torch.stack([R.preprocess_u8(t, 416) for t in tiles])
+    with torch.no_grad():
+        ref32 = R.darknet_forward(blocks, sd, x).numpy()
+    # the checkpoint is bimodal in BOTH evaluations: nothing between conf 0.1 and 0.8, exactly the planted rows above
+    for dec in (ref32, dec_gpu):
+        c = dec[..., 4]
+        assert ((c >= 0.1) & (c < 0.85)).sum() == 0
+        assert [(c[b] >= 0.8).sum() for b in range(B)] == [len(t) for t in truth]
+    want = [_oracle_final(ref32[b]) for b in range(B)]
+    rate, total = _two_way_rate(got, want)
+    print("bf16, planted checkpoint: %d final rows (both sides), two-way match at IoU>=0.99: %.4f" % (total, rate))
+    assert total >= 60
+    assert rate >= MATCH_BAR
+    # and post-processing is bit-exact on the GPU's own decoded tensor
+    for b in range(B):
+        mine = _oracle_final(dec_gpu[b])
+        assert got[b] is not None and np.array_equal(bits(got[b]), bits(mine)), b
+
+
+def test_final_detections_bar_fp32_mode_gaussian_checkpoint(dev):
+    """precision = "fp32": the bar must hold on ANY checkpoint, including the seeded Gaussian one whose passing rows
+    all sit in the tail next to the threshold (~450 candidates per tile on the 26-grid)."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    cfg = ensure_cfg("yolov3-custom")
+    m, sd = _model(cfg, seed=1, conf_bias=(-6.0, -1.5, -6.0), wh_gain=0.15)
+    m.precision = "fp32"
+    blocks = R.parse_cfg(cfg)
+    B = 2
+    tiles = synth.synthetic_tiles(B, size=1536, seed=9)
+    det = TileDetector(m, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=B, cap=1024, device=dev)
+    assert det.engine.precision == "fp32"
+    got = det.detect(torch.from_numpy(tiles))
+    x = torch.stack([R.preprocess_u8(t, 416) for t in tiles])
+    with torch.no_grad():
+        ref32 = R.darknet_forward(blocks, sd, x).numpy()
+    want = [_oracle_final(ref32[b]) for b in range(B)]
+    rate, total = _two_way_rate(got, want)
+    print("fp32 mode, Gaussian checkpoint: %d final rows (both sides), two-way match at IoU>=0.99: %.4f" % (total, rate))
+    assert total >= 100
+    assert rate >= MATCH_BAR
+
+
+# ------------------------------------------------------------------ the benched batch sizes
+def _random_tiles(batch, size, seed):
+    rng = np.random.default_rng([seed, batch, size])
+    return torch.from_numpy(rng.integers(0, 256, size=(batch, size, size, 3), dtype=np.uint8))
+
+
+@pytest.mark.parametrize("name,batch,probe,sample", [("yolov3-custom", 256, (5, 255), (0, 100, 255)),
+                                                      ("yolov3-tiny", 64, (3, 63), (0, 63))])
+def test_forward_at_benched_batch(name, batch, probe, sample, dev):
+    """BASELINE configs C3 (custom, B = 256) and C2 (tiny, B = 64): layer 0 alone has 44.7 M padded rows at B = 256 and
+    the kernel addresses them with 32-bit row indices and multiply-shift divisions.  Tiles deep in the batch must give
+    the bits they give alone (B = 1), and a sample of tiles must meet the raw-head bar against the fp32 oracle."""
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    cfg = ensure_cfg(name)
+    m, sd = _model(cfg, seed=2, conf_bias=-2.0)
+    blocks = R.parse_cfg(cfg)
+    tiles = _random_tiles(batch, 416, seed=21)
+    eng = m.engine(device=dev, max_batch=batch)
+    assert eng.max_batch >= batch
+    full = eng.forward_u8(tiles)
+    eng.check()
+    assert torch.isfinite(full).all()
+    for t in probe:
+        one = eng.forward_u8(tiles[t:t + 1])
+        eng.check()
+        assert torch.equal(full[t].view(torch.int32), one[0].view(torch.int32)), "tile %d of %d differs from its B=1 result" % (t, batch)
+    idx = list(sample)
+    x = torch.stack([R.preprocess_u8(tiles[t].numpy(), 416) for t in idx])
+    with torch.no_grad():
+        _, raw32 = R.darknet_forward(blocks, sd, x, return_raw_heads=True)
+    err = raw_head_error(full[idx].cpu(), raw32, blocks)
+    print("%s at B=%d: raw heads of tiles %s vs fp32 oracle: %.3e" % (name, batch, idx, err))
+    assert err <= 2e-2
+
+
+def test_nms_at_benched_batch(dev):
+    """BASELINE config C5: 128 tiles x 10 647 rows, conf 0.01 (every row a candidate).  Keep indices and merged rows of
+    tiles sampled across the batch are bit-exact against the oracle."""
+    from amyloid_yolo_paper_b200 import _lib, synth
+    from amyloid_yolo_paper_b200.utils.utils import non_max_suppression_device
+    base = synth.synthetic_predictions(8, seed=5)
+    B = 128
+    P = np.concatenate([base] * (B // 8), 0)
+    P[100] = synth.synthetic_predictions(1, seed=77)[0]            # one tile that exists nowhere else in the batch
+    pred = torch.from_numpy(P).to(dev)
+    rows, keep, counts = non_max_suppression_device(pred, 0.01, 0.4)
+    lib, ctx = _lib.load(), _lib.context(0)
+    _lib.check(lib.ay_check(ctx, ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+    counts_h = counts.cpu().numpy()
+    assert (counts_h > 1000).all()
+    for b in (0, 37, 100, 127):
+        want_rows, want_keep = R.nms_exact(P[b], 0.01, 0.4)
+        k = int(counts_h[b])
+        assert k == len(want_keep), b
+        assert np.array_equal(keep[b, :k].cpu().numpy(), want_keep), "keep indices of tile %d" % b
+        assert np.array_equal(bits(rows[b, :k]), bits(want_rows)), "merged rows of tile %d" % b
+    # copies of the same tile at different batch positions agree bit for bit
+    assert torch.equal(rows[5, :int(counts_h[5])].view(torch.int32), rows[125, :int(counts_h[125])].view(torch.int32))
+    assert np.array_equal(bits(pred[100, :, :4]), bits(R.xywh2xyxy(P[100, :, :4])))
+
+
+# ------------------------------------------------------------------ advisor findings (round 1)
+def test_detector_survives_engine_replacement(dev):
+    """A TileDetector must never run on a destroyed context: model(x) with a batch above the detector's capacity makes
+    Darknet rebuild its engine; so does a weight reload.  (Round 1 cached the raw ay_ctx pointer: use-after-free.)"""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    m, sd = _model(ensure_cfg("yolov3-tiny"), seed=0, conf_bias=1.0)
+    det = TileDetector(m, conf_thres=0.5, nms_thres=0.4, merge_boxes=False, max_batch=4, cap=2535, device=dev)
+    tiles = _random_tiles(4, 416, seed=3)
+    first = det.detect(tiles.to(dev))
+    old = det.engine
+    y = m(torch.rand(8, 3, 416, 416))                               # batch 8 > 4: a new, larger engine replaces the old one
+    assert y.shape[0] == 8 and m._engine is not old
+    again = det.detect(tiles.to(dev))
+    assert det.engine is m._engine and det.engine.max_batch >= 8
+    for a, b in zip(first, again):
+        assert (a is None) == (b is None) and (a is None or torch.equal(a, b))
+    # in-place weight change: the detector picks up the re-folded weights
+    with torch.no_grad():
+        for p in m.parameters():
+            p.mul_(1.0)                                             # bumps every version counter, values unchanged
+    before = det.engine
+    third = det.detect(tiles.to(dev))
+    assert det.engine is not before
+    for a, b in zip(first, third):
+        assert (a is None) == (b is None) and (a is None or torch.equal(a, b))
+    # .data writes are invisible to autograd's version counters: invalidate_engine() is the documented way
+    m.module_list[0][0].weight.data.mul_(0.5)
+    m.invalidate_engine()
+    changed = det.detect(tiles.to(dev))
+    assert any((a is None) != (b is None) or (a is not None and not torch.equal(a, b)) for a, b in zip(first, changed))
+
+
+def test_img_size_other_than_cfg_height(dev):
+    """detect.py --img_size: the reference resizes to opt.img_size, runs the network at that size (models.py:238) and
+    rescales with it (detect.py:129).  Round 1 silently ran at the cfg's 416."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.models import Darknet
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    cfg = ensure_cfg("yolov3-custom")
+    S = 320
+    m = Darknet(cfg, img_size=S)
+    sd = synth.synthetic_state_dict(m, seed=1, conf_bias=(-6.0, -1.5, -6.0), wh_gain=0.15)
+    blocks = R.parse_cfg(cfg)
+    B = 2
+    tiles = synth.synthetic_tiles(B, size=1000, seed=4)
+    det = TileDetector(m, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=B, cap=512, device=dev)
+    assert det.img_size == S and det.engine.img_size == S and det.rows == 3 * (10 * 10 + 20 * 20 + 40 * 40)
+    got = det.detect(torch.from_numpy(tiles))
+    dec = det.engine.forward_u8(torch.from_numpy(tiles)).cpu()
+    det.check()
+    x = torch.stack([R.preprocess_u8(t, S) for t in tiles])
+    with torch.no_grad():
+        ref, raw = R.darknet_forward(blocks, sd, x, return_raw_heads=True)
+    assert dec.shape == ref.shape
+    assert raw_head_error(dec, raw, blocks, img_dim=S) <= 2e-2
+    n = 0
+    for b in range(B):
+        want = _oracle_final(dec[b].numpy(), size=S, orig=(1000, 1000))
+        assert (got[b] is None) == (len(want) == 0)
+        if got[b] is not None:
+            assert np.array_equal(bits(got[b]), bits(want)), b
+            n += len(want)
+    assert n > 0
+    # Darknet.forward takes the size from the tensor, like the reference
+    y = m(x)
+    assert np.array_equal(bits(y), bits(dec))
+
+
+def test_merge_reports_non_finite_rows(dev):
+    """A non-finite field in a kept detection made the tuple hash of round 1 spin forever (frexp(inf) = inf).  The
+    reference raises at int(inf) / int(nan) (core.py:330-337); here the call fails loudly at the next check."""
+    from amyloid_yolo_paper_b200 import _lib, synth
+    from amyloid_yolo_paper_b200.core import merge_detections_device
+    rows = np.zeros((3, 8, 7), np.float32)
+    counts = np.array([4, 4, 4], np.int32)
+    for b in range(3):
+        rows[b, :4] = synth.synthetic_detections(4, seed=60 + b)
+    rows[1, 2, 2] = np.inf
+    rows[2, 0, 4] = np.nan
+    out, oc = merge_detections_device(torch.from_numpy(rows).to(dev), torch.from_numpy(counts).to(dev), 416, (1536, 1536))
+    lib, ctx = _lib.load(), _lib.context(0)
+    code = lib.ay_check(ctx, ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    assert code == -1 and b"non-finite" in lib.ay_last_error()
+    oc = oc.cpu().numpy()
+    assert oc[0] > 0 and oc[1] == -1 and oc[2] == -1
+    assert lib.ay_check(ctx, ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)) == 0     # flag is cleared
+
+
+def test_several_contexts_in_one_process(dev):
+    """Two engines (two ay_ctx) in one process, plus the per-GPU utility context: NMS with its 128 KB shared-memory
+    opt-in runs through each (round 1 cached the opt-in in a process-wide static; it is per device).  With a second
+    GPU present the same is done there."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    from amyloid_yolo_paper_b200.utils.utils import non_max_suppression
+    P = synth.synthetic_predictions(1, seed=31)
+    want_rows, want_keep = R.nms_exact(P[0], 0.3, 0.4)
+    devices = [dev] + ([torch.device("cuda", 1)] if torch.cuda.device_count() > 1 else [])
+    for d in devices:
+        ma, _ = _model(ensure_cfg("yolov3-tiny"), seed=0, conf_bias=1.0)
+        mb, _ = _model(ensure_cfg("yolov3-tiny"), seed=1, conf_bias=1.0)
+        da = TileDetector(ma, conf_thres=0.5, merge_boxes=False, max_batch=2, cap=2535, device=d)
+        db = TileDetector(mb, conf_thres=0.5, merge_boxes=False, max_batch=2, cap=2535, device=d)
+        assert da.ctx.value != db.ctx.value
+        tiles = _random_tiles(2, 416, seed=8).to(d)
+        ra, rb = da.detect(tiles), db.detect(tiles)
+        assert len(ra) == 2 and len(rb) == 2
+        out, keep = non_max_suppression(torch.from_numpy(P.copy()).to(d), 0.3, 0.4, return_keep=True)
+        assert np.array_equal(keep[0].numpy(), want_keep) and np.array_equal(bits(out[0]), bits(want_rows))

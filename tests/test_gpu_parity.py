@@ -238,7 +238,7 @@ def test_forward_mini_vs_reference_golden(golden, dev):
 def test_forward_full_networks_vs_oracle(name, batch, dev):
     """Decoded head outputs of the whole network vs the fp32 oracle (tolerance 2e-2, bf16 storage)
     and, layer by layer, vs the oracle that rounds activations to bf16 at the same points."""
-    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200 import _lib, synth
     from amyloid_yolo_paper_b200.config import ensure_cfg
     cfg = ensure_cfg(name)
     m, sd = _model(cfg, seed=1, conf_bias=-2.0)
@@ -265,8 +265,9 @@ def test_forward_full_networks_vs_oracle(name, batch, dev):
             continue
         try:
             lay = eng.layer_output(i, batch).cpu()
-        except Exception:
-            continue                                                        # fused away (no stored output)
+        except _lib.EngineError as e:
+            assert "no stored output" in str(e), e                          # fused away; anything else is a failure
+            continue
         worst = max(worst, rel_max(lay, emu_layers[i]))
     assert worst <= BF16_TOL, "per-layer activations vs bf16-emulating oracle"
     # the tensor-core kernel against the plain CUDA-core convolution over the same buffers
@@ -490,7 +491,7 @@ def test_pipeline_end_to_end_vs_oracle_chain(dev):
 
 
 @pytest.mark.parametrize("toggle", ["AY_NO_RESIDENT", "AY_NO_PACKED", "AY_NO_MBATCH", "AY_NO_UPFUSE", "AY_NO_HEADSTAGE",
-                                    "AY_ONE_UNIT", "AY_FULL_K"])
+                                    "AY_ONE_UNIT", "AY_FULL_K", "AY_NO_PDL", "AY_NO_HEADFAST"])
 def test_forward_plan_variants_agree(toggle, dev):
     """Every planning shortcut of the convolution engine (resident weights, packed stride-2 operand, row-batched first
     layer, fused upsample, staged head stores, multi-unit stages) can be switched off at ay_net_build time; the plain
@@ -520,7 +521,7 @@ def test_forward_plan_variants_agree(toggle, dev):
     ra, rb = decoded_to_raw(base, blocks), decoded_to_raw(other, blocks)
     worst = max(float(((a - b).abs() * (b.abs() < 12)).max() / b.abs().max()) for a, b in zip(ra, rb))
     assert worst <= BF16_TOL, "%s: raw heads differ by %.3e" % (toggle, worst)
-    if toggle in ("AY_NO_UPFUSE", "AY_NO_HEADSTAGE", "AY_ONE_UNIT", "AY_NO_RESIDENT", "AY_FULL_K"):
+    if toggle in ("AY_NO_UPFUSE", "AY_NO_HEADSTAGE", "AY_ONE_UNIT", "AY_NO_RESIDENT", "AY_FULL_K", "AY_NO_PDL"):
         assert np.array_equal(bits(base), bits(other)), "%s changes only data movement: results must be bit-identical" % toggle
 
 
