@@ -172,7 +172,7 @@ struct NmsScratch {
 size_t nms_scratch_bytes(int batch, int n_rows);
 int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres,
                float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap,
-               void* scratch, size_t scratch_bytes, unsigned int* err_flag, cudaStream_t s);
+               void* scratch, size_t scratch_bytes, unsigned int* err_flag, cudaStream_t s, cudaEvent_t* ev = nullptr);
 size_t merge_scratch_bytes(int batch, int cap);
 int launch_rescale_merge(const float* rows, const int32_t* counts, int batch, int cap,
                          float pad_x_half, float pad_y_half, float unpad_w, float unpad_h,

@@ -1185,6 +1185,29 @@ extern "C" int ay_nms(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_cla
                         ctx->nms_scratch, ctx->nms_bytes, ctx->err_flag, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int ay_nms_timed(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes, float conf_thres,
+                            float nms_thres, float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream,
+                            float* ms4_h) {
+  AY_ENTER(ctx);
+  if (!pred || !out_rows || !out_keep || !out_counts || !ms4_h || batch < 1 || n_rows < 1) {
+    set_error("ay_nms_timed: bad arguments");
+    return AY_EINVAL;
+  }
+  AY_TRY(ensure_scratch(&ctx->nms_scratch, &ctx->nms_bytes, ay::nms_scratch_bytes(batch, n_rows)));
+  cudaEvent_t ev[5];
+  for (int i = 0; i < 5; ++i) AY_CUDA(cudaEventCreate(&ev[i]));
+  int rc = ay::launch_nms(pred, batch, n_rows, n_classes, conf_thres, nms_thres, out_rows, out_keep, out_counts, cap,
+                          ctx->nms_scratch, ctx->nms_bytes, ctx->err_flag, static_cast<cudaStream_t>(stream), ev);
+  if (rc == AY_OK && cudaStreamSynchronize(static_cast<cudaStream_t>(stream)) != cudaSuccess) {
+    set_error("ay_nms_timed: stream failed");
+    rc = AY_ECUDA;
+  }
+  for (int i = 0; rc == AY_OK && i < 4; ++i)
+    if (cudaEventElapsedTime(&ms4_h[i], ev[i], ev[i + 1]) != cudaSuccess) { set_error("ay_nms_timed: event timing failed"); rc = AY_ECUDA; }
+  for (int i = 0; i < 5; ++i) cudaEventDestroy(ev[i]);
+  return rc;
+}
+
 extern "C" int ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* counts, int batch, int cap,
                                 int current_dim, int orig_h, int orig_w, int merge, float* out_rows,
                                 int32_t* out_counts, void* stream) {

@@ -371,7 +371,7 @@ size_t nms_scratch_bytes(int batch, int n_rows) { return make_layout(batch, n_ro
 
 int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres, float* out_rows,
                int32_t* out_keep, int32_t* out_counts, int cap, void* scratch, size_t scratch_bytes,
-               unsigned int* err_flag, cudaStream_t s) {
+               unsigned int* err_flag, cudaStream_t s, cudaEvent_t* ev) {
   if (n_rows > kMaxRows) {
     set_error("nms: %d rows per tile exceed the on-chip sort capacity of %d", n_rows, kMaxRows);
     return AY_EINVAL;
@@ -391,14 +391,20 @@ int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thr
   // per launch, like conv_gemm: the attribute is per DEVICE (a process may drive several GPUs) and setting it is cheap
   AY_CUDA(cudaFuncSetAttribute(nms_prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
   uint8_t* sc = static_cast<uint8_t*>(scratch);
+  // ev (ay_nms_timed only): five events bracketing the four kernels
+  if (ev) AY_CUDA(cudaEventRecord(ev[0], s));
   nms_prepare_kernel<<<batch, kSortThreads, sort_smem, s>>>(pred, n_rows, n_classes, conf_thres, sc, L);
   AY_CUDA(cudaGetLastError());
+  if (ev) AY_CUDA(cudaEventRecord(ev[1], s));
   nms_mask_kernel<<<dim3(96, batch), 64, 0, s>>>(n_rows, nms_thres, sc, L);
   AY_CUDA(cudaGetLastError());
+  if (ev) AY_CUDA(cudaEventRecord(ev[2], s));
   nms_sweep_kernel<<<batch, 32, 0, s>>>(n_rows, sc, L);
   AY_CUDA(cudaGetLastError());
+  if (ev) AY_CUDA(cudaEventRecord(ev[3], s));
   nms_cluster_kernel<<<dim3(16, batch), 128, 0, s>>>(n_rows, sc, L, out_rows, out_keep, out_counts, cap, err_flag);
   AY_CUDA(cudaGetLastError());
+  if (ev) AY_CUDA(cudaEventRecord(ev[4], s));
   return AY_OK;
 }
 

@@ -2,19 +2,21 @@
 
     python -m amyloid_yolo_paper_b200.detect --image_folder tiles/ --model_def <cfg> \
         --weights_path checkpoints/yolov3_ckpt_105.pth --class_path data/custom/classes.names \
-        --conf_thres 0.8 --nms_thres 0.4 --img_size 416 --merge_boxes True
+        --conf_thres 0.8 --nms_thres 0.4 --img_size 416 --batch_size 64 --n_cpu 8 --merge_boxes True
 
-Same flags, defaults and string-boolean convention (``--merge_boxes`` is compared with
-``"True"``, ``detect.py:132``).  Differences, all outside the numeric path: nothing is drawn
-(the reference's matplotlib output, ``detect.py:108-171``, is left out); detections are
-printed like the reference prints them and written to ``output/detections.json``; the
-CAA-classifier flags are accepted and rejected with a clear message (out of scope,
-SURVEY.md §2).  Images are decoded on the host with PIL exactly like
-``utils/datasets.py:45-59``; ToTensor + Resize run on the GPU inside the first
-convolution.
+Same flags, defaults and string-boolean convention (``--merge_boxes`` is compared with ``"True"``,
+``detect.py:132``).  ``--img_size`` is the network input size exactly as in the reference (``Darknet(...,
+img_size)``, ``Resize(opt.img_size)``, ``rescale_boxes(..., opt.img_size, ...)``: detect.py:59,73,129), any multiple
+of 32; ``--batch_size`` and ``--n_cpu`` size the batches and the decode workers of the loader
+(``utils/datasets.py``), which hands pinned uint8 blocks of the 416^2 sampled pixels to one
+H2D / compute / D2H pipeline (``TileDetector.detect_stream``).
+
+Differences, all outside the numeric path: nothing is drawn (the reference's matplotlib output,
+``detect.py:108-171``, is left out); detections are printed like the reference prints them and written to
+``<output>/detections.json``; the CAA-classifier flags are accepted and rejected with a clear message (out of
+scope).
 """
 import argparse
-import glob
 import json
 import os
 import time
@@ -24,6 +26,7 @@ import torch
 
 from .models import Darknet
 from .pipeline import TileDetector
+from .utils.datasets import TileLoader, load_image  # noqa: F401  (load_image re-exported for callers of round 1)
 from .utils.utils import load_classes
 
 
@@ -59,12 +62,6 @@ def pad_square(img):
     return out
 
 
-def load_image(path):
-    """utils/datasets.py:47-50."""
-    from PIL import Image
-    return np.array(Image.open(path).convert("RGB"), dtype=np.uint8)
-
-
 def load_model(opt, device):
     model = Darknet(opt.model_def, img_size=opt.img_size).to(device)
     if opt.weights_path.endswith(".weights"):
@@ -80,27 +77,30 @@ def run(opt):
         raise SystemExit("the CAA-classifier post-filter (core.py:425-480) is outside this build's scope")
     if not torch.cuda.is_available():
         raise SystemExit("no CUDA device: this detect.py runs on the B200 engine only (no CPU fallback)")
+    if opt.img_size < 32 or opt.img_size % 32 != 0:
+        raise SystemExit("--img_size must be a positive multiple of 32 (got %d)" % opt.img_size)
     device = torch.device("cuda", torch.cuda.current_device())
     os.makedirs(opt.output, exist_ok=True)
     model = load_model(opt, device)
     classes = load_classes(opt.class_path) if opt.class_path and os.path.exists(opt.class_path) else None
-    files = sorted(glob.glob("%s/*.*" % opt.image_folder))
-    det = TileDetector(model, conf_thres=opt.conf_thres, nms_thres=opt.nms_thres,
-                       merge_boxes=(opt.merge_boxes == "True"), max_batch=max(1, opt.batch_size), device=device)
-    results = {}
+    batch = max(1, opt.batch_size)
+    det = TileDetector(model, conf_thres=opt.conf_thres, nms_thres=opt.nms_thres, merge_boxes=(opt.merge_boxes == "True"),
+                       max_batch=batch, device=device, img_size=opt.img_size)
+    loader = TileLoader(opt.image_folder, img_size=opt.img_size, batch_size=batch, n_cpu=opt.n_cpu)
+    results, order = {}, []
+
+    def batches():                                # (pinned uint8 [b,S,S,3], original (h, w)) per loader batch
+        for paths, tiles, shape in loader:
+            order.append(paths)
+            yield tiles, shape
+
     print("\nPerforming object detection:")
     prev = time.time()
-    for b0 in range(0, len(files), max(1, opt.batch_size)):
-        paths = files[b0:b0 + max(1, opt.batch_size)]
-        imgs = [load_image(p) for p in paths]
-        # images of one batch may differ in size: group by padded size so each group is one tensor
-        for p, img in zip(paths, imgs):
-            sq = pad_square(img)
-            tiles = torch.from_numpy(sq[None]).pin_memory()
-            out = det.detect(tiles, original_shape=img.shape[:2])[0]
+    for bi, outs in enumerate(det.detect_stream(batches())):
+        for p, out in zip(order[bi], outs):
             results[p] = [] if out is None else out.tolist()
         now = time.time()
-        print("\t+ Batch %d, Inference Time: %.4fs" % (b0 // max(1, opt.batch_size), now - prev))
+        print("\t+ Batch %d, Inference Time: %.4fs" % (bi, now - prev))
         prev = now
     for p, rows in results.items():
         print("Image: '%s'" % p)

@@ -182,7 +182,8 @@ class TileDetector:
 
     def detect_stream(self, batches, original_shape=None):
         """``batches``: iterable of HOST tensors (ideally pinned; uint8 [B,H,H,3] or fp32 [B,3,S,S], any B each) - what
-        ``detect.py:88-95`` pulls from its DataLoader.  Yields, per batch and in order, the list ``detect()`` returns.
+        ``detect.py:88-95`` pulls from its DataLoader - or of ``(tensor, (h, w))`` pairs when the original image shape
+        differs per batch (``utils.datasets.TileLoader``).  Yields, per batch and in order, the list ``detect()`` returns.
 
         One software pipeline runs across the whole iterable: sub-batches are uploaded on a copy stream into two device
         buffers while the previous one computes, results come back on a third stream from two result slots and are
@@ -198,19 +199,20 @@ class TileDetector:
         self.d2h_bytes = 0
 
         def work():                                   # (batch index, tiles, lo, hi, last span of its batch)
-            for bi, tiles in enumerate(batches):
+            for bi, item in enumerate(batches):
+                tiles, shape = item if isinstance(item, tuple) else (item, original_shape)
                 if tiles.is_cuda:
                     raise ValueError("detect_stream takes host batches; use detect() for device tensors")
                 spans = self._plan_spans(tiles.shape[0], stream_head=(bi == 0))
                 for k, (lo, hi) in enumerate(spans):
-                    yield bi, tiles, lo, hi, k == len(spans) - 1
+                    yield bi, tiles, lo, hi, k == len(spans) - 1, shape
                 if not spans:
-                    yield bi, tiles, 0, 0, True
+                    yield bi, tiles, 0, 0, True, shape
 
         copied, computed, fetched = {}, {}, {}
 
         def upload(i, item):
-            _, tiles, lo, hi, _ = item
+            _, tiles, lo, hi, _, _ = item
             shape = (self.max_batch,) + tuple(tiles.shape[1:])
             buf = self._stage[i % 2]
             if buf is None or buf.shape != shape or buf.dtype != tiles.dtype:
@@ -260,7 +262,7 @@ class TileDetector:
             if i - 2 in fetched:
                 main.wait_event(fetched[i - 2])      # result slot i % 2 has been read back
             if n > 0:
-                self.run_device(self._stage[i % 2][:n], original_shape, slot=i % 2)
+                self.run_device(self._stage[i % 2][:n], cur[5], slot=i % 2)
             ev = torch.cuda.Event()
             ev.record(main)
             computed[i] = ev

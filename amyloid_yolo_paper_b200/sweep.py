@@ -81,22 +81,44 @@ def sweep(detector, tile_source, n_tiles, batch, group=None, gather=True):
     """Run ``detector`` (a :class:`TileDetector`) over this rank's shard of ``n_tiles``.
 
     ``tile_source(lo, hi)`` returns the tiles ``[lo, hi)`` as a uint8 ``[hi-lo,H,H,3]`` tensor
-    (host or device).  -> (rows, counts) of the whole sweep if ``gather`` else of the shard."""
+    (host or device).  -> (rows, counts) of the whole sweep if ``gather`` else of the shard.
+
+    Device tiles stay on the device end to end: every batch's result rows are appended to one shard buffer on the
+    compute stream (no host round trip per batch), the row padding is trimmed to the shard's longest list with a
+    single read-back at the end, and the gather moves ``[tiles, kmax, 7]`` once per sweep (config C4)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     lo, hi = shard_range(n_tiles, rank, world)
-    per_tile = []
+    nccl = dist.is_initialized() and dist.get_backend(group) == "nccl"
     batches = (tile_source(b0, min(hi, b0 + batch)) for b0 in range(lo, hi, batch))
     first = next(batches, None)
-    if first is not None and not first.is_cuda:
-        # host tiles: one software pipeline over the whole shard (upload of batch k+1 under the compute of batch k)
-        for outs in detector.detect_stream(itertools.chain([first], batches)):
-            per_tile.extend(outs)
-    elif first is not None:
+    if first is not None and first.is_cuda:
+        cap = detector.cap
+        rows = torch.zeros((hi - lo, cap, 7), dtype=torch.float32, device=detector.device)
+        counts = torch.zeros((hi - lo,), dtype=torch.int32, device=detector.device)
+        at = 0
         for tiles in itertools.chain([first], batches):
-            per_tile.extend(detector.detect(tiles))
-    dev = detector.device if (dist.is_initialized() and dist.get_backend(group) == "nccl") else None
-    rows, counts = pack_detections(per_tile, device=dev)
+            n = tiles.shape[0]
+            r, c = detector.run_device(tiles)
+            rows[at:at + n].copy_(r)
+            counts[at:at + n].copy_(c)
+            at += n
+        detector.check()                                   # capacity overflows / device faults surface here
+        kmax = max(int(counts.max().item()), 1) if hi > lo else 1
+        rows = rows[:, :kmax].contiguous()
+        # rows beyond a tile's count hold whatever the previous occupant of the slot left: zero them so that the
+        # gathered block is a function of the detections only
+        valid = torch.arange(kmax, device=rows.device).view(1, -1) < counts.view(-1, 1)
+        rows = torch.where(valid.unsqueeze(-1), rows, torch.zeros((), dtype=rows.dtype, device=rows.device))
+        if not nccl and dist.is_initialized():
+            rows, counts = rows.cpu(), counts.cpu()
+    else:
+        per_tile = []
+        if first is not None:
+            # host tiles: one software pipeline over the whole shard (upload of batch k+1 under the compute of batch k)
+            for outs in detector.detect_stream(itertools.chain([first], batches)):
+                per_tile.extend(outs)
+        rows, counts = pack_detections(per_tile, device=detector.device if nccl else None)
     if gather and world > 1:
         return allgather_detections(rows, counts, n_tiles, group)
     return rows, counts

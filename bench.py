@@ -1,29 +1,31 @@
 #!/usr/bin/env python
 """Benchmark of the tile-detection hot path (BASELINE.json metric: tiles/sec).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c3|c1|c2|c5]
 
-Workload (config C3/C4 of BASELINE.json): yolov3-custom (Darknet-53, 2 classes), synthetic
-1536x1536 uint8 WSI tiles, nearest-resized to 416 inside the first convolution, bf16 tensor-core
-forward + fused YOLO decode + cluster-merging NMS (conf 0.8, nms 0.4) + rescale_boxes +
-mergeDetections.  One step = one batch of B tiles per GPU through that whole chain.
+Workloads (BASELINE.json `configs`; default c3, which is also C4 when N > 1):
+  c3  yolov3-custom (Darknet-53, 2 classes), synthetic 1536x1536 uint8 WSI tiles nearest-resized to 416 inside the
+      first convolution, bf16 tensor-core forward + fused YOLO decode + cluster-merging NMS (conf 0.8, nms 0.4) +
+      rescale_boxes + mergeDetections, B = 256 tiles per GPU per step.  With N > 1 the tiles are sharded by rank through
+      ``sweep.sweep`` and the detection lists are all-gathered over NCCL once per sweep (config C4).
+  c1  the same network at B = 1 (the shape of the reference's only benchmark loop, validation.py:282-366).
+  c2  yolov3-tiny (80 classes), fp32 [64,3,416,416] inputs, B = 64.
+  c5  NMS stress: ay_nms alone on 128 tiles x 10 647 decoded rows, conf_thres 0.01 (every row a candidate).
 
-* ``value``  - tiles/s with the uint8 tiles already resident in HBM (device-timed, CUDA events,
-               max over ranks).  Per-GPU work is fixed as N grows ("weak"); with N > 1 each step
-               ends with the NCCL all-gather of the step's detection lists (config C4).
-* ``e2e``    - the same metric through the reference-facing API with HOST buffers
-               (``TileDetector.detect`` on a pinned fp32 [B,3,416,416] batch = the tensor
-               ``Darknet.forward`` receives in detect.py:94): H2D + chain + D2H of the detections
-               inside the timed region.
-* ``roofline`` - conv stack (``ay_forward``: 74 tcgen05 implicit-GEMM launches + first-layer and
-               gather kernels) FLOPs / its CUDA-event time vs the measured bf16 peak.
-* ``cpu_baseline`` - the oracle port of the reference path (torch CPU forward + python NMS loop +
-               pixel-set mergeDetections) on a bounded sample, all host threads.
-
-``--impl reference`` times that CPU path as the reference arm (the reference is pure Python and
-is not present on the GPU box).
+One JSON line:
+* ``value``    - tiles/s with the inputs already resident in HBM (CUDA events on the launching stream, max over ranks).
+* ``e2e``      - the same metric through the reference-facing API with HOST buffers, host<->device copies inside the
+                 timed region (c3: ``TileDetector.detect_stream`` over pinned uint8 [B,416,416,3] batches - the 416^2
+                 pixels the resize samples, gathered by the loader; the fp32 [B,3,416,416] format is reported beside it).
+* ``roofline`` - c1-c3: the conv stack (``ay_forward``) FLOPs / its CUDA-event time vs the measured bf16 peak;
+                 c5: the IoU bit-mask kernel's algorithmic bytes / its CUDA-event time vs the measured HBM peak.
+* ``cpu_baseline`` - the reference's own CPU implementation of the path on a bounded sample, all host threads:
+                 the UNMODIFIED reference modules when ``oracle/_ref/reference_py.zip`` (or the checkout) is present
+                 (kind "reference"), else the oracle port (kind "port").
+``--impl reference`` times that CPU path as its own arm.
 """
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -37,6 +39,12 @@ if ROOT not in sys.path:
 
 FLOP_PER_TILE = {"yolov3-custom": 65297143808, "yolov3-tiny": 5564961792}   # SURVEY.md §8(d), convs only
 METRIC = "tiles/sec (416^2 YOLOv3 conv+decode+NMS)"
+CONFIGS = {
+    "c3": {"net": "yolov3-custom", "batch": 256, "conf_bias": "-6,-6,0.62", "cpu_tiles": 8, "ref_tiles": 4},
+    "c1": {"net": "yolov3-custom", "batch": 1, "conf_bias": "-6,-6,0.62", "cpu_tiles": 1, "ref_tiles": 1},
+    "c2": {"net": "yolov3-tiny", "batch": 64, "conf_bias": "-4,-0.38", "cpu_tiles": 16, "ref_tiles": 8},
+    "c5": {"net": None, "batch": 128, "conf_bias": "", "cpu_tiles": 2, "ref_tiles": 1},
+}
 
 
 def parse_args():
@@ -45,16 +53,22 @@ def parse_args():
     p.add_argument("--steps", type=int, default=10)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", type=str, default="ours", choices=["ours", "reference"])
-    p.add_argument("--batch", type=int, default=256, help="tiles per GPU per step")
-    p.add_argument("--net", type=str, default="yolov3-custom", choices=sorted(FLOP_PER_TILE))
+    p.add_argument("--config", type=str, default="c3", choices=sorted(CONFIGS))
+    p.add_argument("--batch", type=int, default=0, help="tiles per GPU per step (default: the config's)")
+    p.add_argument("--net", type=str, default="", choices=[""] + sorted(FLOP_PER_TILE))
     p.add_argument("--tile", type=int, default=1536, help="source tile edge (uint8 HWC)")
-    p.add_argument("--conf_bias", type=str, default="-6,-6,0.62",
-                   help="objectness bias of the synthetic checkpoint per head (grids 13,26,52): a few dozen candidates per "
-                        "tile at conf 0.8, mostly small boxes as in the reference's plaque data")
-    p.add_argument("--cpu-sample", type=int, default=8, help="tiles in the bounded CPU-baseline sample (about 2 s each)")
+    p.add_argument("--conf_bias", type=str, default="",
+                   help="objectness bias of the synthetic checkpoint per head: a few dozen candidates per tile at conf 0.8, "
+                        "mostly small boxes as in the reference's plaque data")
+    p.add_argument("--cpu-sample", type=int, default=0, help="tiles in the bounded CPU-baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
-    p.add_argument("--layers", action="store_true", help="also print a per-layer timing table to stderr")
-    return p.parse_args()
+    p.add_argument("--no-e2e", action="store_true", help="device-resident value and roofline only (short runs under ncu)")
+    args = p.parse_args()
+    cfg = CONFIGS[args.config]
+    args.net = args.net or cfg["net"]
+    args.batch = args.batch or cfg["batch"]
+    args.conf_bias = args.conf_bias or cfg["conf_bias"]
+    return args
 
 
 def measured_peaks():
@@ -62,7 +76,7 @@ def measured_peaks():
     if os.path.exists(path):
         d = json.load(open(path))
         return {"bf16": float(d.get("bf16_tflops_sustained") or d["bf16_tflops"]), "bf16_burst": float(d["bf16_tflops"]),
-                "hbm": float(d["hbm_gbs"]), "source": "MEASURED_PEAKS.json (sustained bf16)"}
+                "hbm": float(d["hbm_gbs"]), "source": "MEASURED_PEAKS.json"}
     return {"bf16": 1400.0, "bf16_burst": 1590.0, "hbm": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
@@ -163,98 +177,262 @@ def build_model(net, conf_bias):
     return cfg, model, sd
 
 
-# ----------------------------------------------------------------------------- CPU path (oracle port)
-def cpu_path_step(blocks, sd, x, conf_thres, nms_thres, orig):
-    """The body of detect.py's loop as the reference runs it on the host (oracle port):
-    forward (models.py:237-255) -> non_max_suppression (utils.py:235-273) -> rescale_boxes
-    (utils.py:36-50) -> mergeDetections with pixel-set enumeration (core.py:326-423)."""
-    import torch
-    from oracle import restate as R
-    with torch.no_grad():
-        dec = R.darknet_forward(blocks, sd, x)
-    dets = R.nms_faithful(dec, conf_thres, nms_thres)
-    n = 0
-    for d in dets:
-        if d is None:
-            continue
-        rows = R.rescale_boxes(d.numpy().copy(), x.shape[2], orig)
-        n += len(R.merge_faithful(rows))
-    return n
+# ----------------------------------------------------------------------------- CPU path (reference / oracle port)
+class CpuPath:
+    """The body of detect.py's loop on the host (detect.py:88-133, validation.py:333-346 without the CAA filter and
+    file I/O): forward -> non_max_suppression -> rescale_boxes -> mergeDetections, tensors already in RAM.
+    kind "reference": the unmodified reference modules (oracle/_ref archive or the mounted checkout);
+    kind "port": the oracle's restatement (oracle/restate.py)."""
+
+    def __init__(self, net, conf_bias):
+        import torch
+        from oracle import ref_import
+        from oracle import restate as R
+        self.R = R
+        self.torch = torch
+        self.cfg, _, self.sd = build_model(net, conf_bias) if net else (None, None, None)
+        self.kind = "port"
+        self.ref = None
+        if ref_import.available():
+            try:
+                self.ref = ref_import.load()
+                self.kind = "reference"
+            except Exception as e:                       # an import problem on the box: fall back to the port, and say so
+                print("reference modules unavailable (%s); timing the oracle port" % e, file=sys.stderr)
+        if net and self.ref is not None:
+            models = self.ref[0]
+            self.model = models.Darknet(self.cfg)
+            self.model.load_state_dict(self.sd)
+            self.model.eval()
+        elif net:
+            self.blocks = R.parse_cfg(self.cfg)
+
+    def step(self, x, conf_thres, nms_thres, orig):
+        torch, R = self.torch, self.R
+        n = 0
+        if self.ref is not None:
+            _, uu, core = self.ref
+            with torch.no_grad():
+                dec = self.model(x)
+                dets = uu.non_max_suppression(dec, conf_thres, nms_thres)
+            for d in dets:
+                if d is None:
+                    continue
+                d = uu.rescale_boxes(d, x.shape[2], orig)
+                n += len(core.mergeDetections(d))
+            return n
+        with torch.no_grad():
+            dec = R.darknet_forward(self.blocks, self.sd, x)
+        for d in R.nms_faithful(dec, conf_thres, nms_thres):
+            if d is None:
+                continue
+            n += len(R.merge_faithful(R.rescale_boxes(d.numpy().copy(), x.shape[2], orig)))
+        return n
+
+    def nms_step(self, pred, conf_thres, nms_thres):
+        if self.ref is not None:
+            out = self.ref[1].non_max_suppression(pred.clone(), conf_thres, nms_thres)
+        else:
+            out = self.R.nms_faithful(pred.clone(), conf_thres, nms_thres)
+        return sum(0 if d is None else len(d) for d in out)
 
 
-def cpu_inputs(net, conf_bias, n_tiles, tile):
+def cpu_inputs(n_tiles, size=416, uniform=False):
     import torch
-    from amyloid_yolo_paper_b200 import synth
-    from oracle import restate as R
-    cfg, model, sd = build_model(net, conf_bias)
-    blocks = R.parse_cfg(cfg)
-    size = int(blocks[0]["height"])
     g = torch.Generator().manual_seed(1234)
+    if uniform:                                 # config C2: fp32 U[0,1) inputs
+        return torch.rand((n_tiles, 3, size, size), generator=g)
     low = torch.rand((n_tiles, 3, 24, 24), generator=g)
     x = torch.nn.functional.interpolate(low, size=(size, size), mode="bilinear")
-    x = ((90.0 + 130.0 * x + 12.0 * torch.randn(x.shape, generator=g)).clamp(0, 255).floor() / 255.0).contiguous()
-    return blocks, sd, x
+    return ((90.0 + 130.0 * x + 12.0 * torch.randn(x.shape, generator=g)).clamp(0, 255).floor() / 255.0).contiguous()
 
 
-def run_cpu_baseline(args, steps, warmup):
+def run_cpu_baseline(args, steps, warmup, tiles_per_step):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    blocks, sd, x = cpu_inputs(args.net, args.conf_bias, args.cpu_sample, args.tile)
-    orig = (args.tile, args.tile)
-    for _ in range(warmup):
-        cpu_path_step(blocks, sd, x[:1], 0.8, 0.4, orig)
+    if args.config == "c5":
+        from amyloid_yolo_paper_b200 import synth
+        path = CpuPath(None, None)
+        pred = torch.from_numpy(synth.synthetic_predictions(tiles_per_step, seed=5))
+        fn = lambda: path.nms_step(pred, 0.01, 0.4)                                    # noqa: E731
+        what = "%d decoded tiles [10647,7], non_max_suppression(0.01, 0.4) only" % tiles_per_step
+        warmup = 0                                                                      # one tile is ~6 s
+    else:
+        path = CpuPath(args.net, args.conf_bias)
+        x = cpu_inputs(tiles_per_step, uniform=args.config == "c2")
+        orig = (416, 416) if args.config == "c2" else (args.tile, args.tile)
+        fn = lambda: path.step(x, 0.8, 0.4, orig)                                       # noqa: E731
+        what = "%d fp32 [3,416,416] tiles, %s forward + NMS(0.8,0.4) + rescale + mergeDetections(pixel sets)" % (
+            tiles_per_step, args.net)
+        for _ in range(warmup):
+            path.step(x[:1], 0.8, 0.4, orig)
     t0 = time.perf_counter()
     dets = 0
     for _ in range(steps):
-        dets += cpu_path_step(blocks, sd, x, 0.8, 0.4, orig)
+        dets += fn()
     dt = time.perf_counter() - t0
-    return {"tiles_per_s": steps * x.shape[0] / dt, "seconds": dt, "cores": cores, "tiles": steps * x.shape[0],
-            "detections": dets}
+    return {"tiles_per_s": steps * tiles_per_step / dt, "seconds": dt, "cores": cores, "tiles": steps * tiles_per_step,
+            "detections": dets, "kind": path.kind, "what": what, "torch": torch.__version__}
 
 
 def reference_arm(args):
-    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference
-    itself is pure Python on torch and is not on the GPU box), all host threads, bounded sample."""
+    """--impl reference: the reference's own CPU implementation of the path, all host threads, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
-    steps, warmup = max(1, args.steps), max(0, min(args.warmup, 3))
-    args.cpu_sample = min(args.cpu_sample, 4)        # about 8 s of host work per step
-    r = run_cpu_baseline(args, steps, min(warmup, 1))
-    sample = "%d steps x %d fp32 [3,416,416] tiles, forward+NMS(0.8,0.4)+rescale+mergeDetections(pixel sets), torch %s" % (
-        steps, args.cpu_sample, torch.__version__)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    per_step = args.cpu_sample or CONFIGS[args.config]["ref_tiles"]
+    r = run_cpu_baseline(args, steps, warmup, per_step)
+    sample = "%d steps x %s, %d warm-up step(s) of 1 tile, torch %s CPU, %d threads" % (
+        steps, r["what"], 0 if args.config == "c5" else warmup, r["torch"], r["cores"])
+    cfg = workload_config(args)
+    cfg["batch_per_gpu"] = per_step                      # what this arm actually ran per step (a bounded sample)
+    cfg["workload"] += " [reference arm: CPU, %d tile(s) per step]" % per_step
     line = {"impl": "reference", "metric": METRIC, "value": r["tiles_per_s"], "unit": "tiles/s", "n_gpus": args.gpus,
-            "steps": steps, "warmup": warmup, "ms_per_step": 1000.0 * r["seconds"] / steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args, cpu=True),
-            "cpu_baseline": {"value": r["tiles_per_s"], "unit": "tiles/s", "cores": r["cores"], "kind": "port",
+            "steps": steps, "warmup": 0 if args.config == "c5" else warmup, "ms_per_step": 1000.0 * r["seconds"] / steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": cfg,
+            "cpu_baseline": {"value": r["tiles_per_s"], "unit": "tiles/s", "cores": r["cores"], "kind": r["kind"],
                              "sample": sample},
             "e2e": {"value": r["tiles_per_s"], "unit": "tiles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, cpu=False):
-    return {"workload": "C3/C4: %s, synthetic %dx%d uint8 tiles nearest-resized to 416, batch %d per GPU, "
-                        "conf_thres 0.8, nms_thres 0.4, merge_boxes" % (args.net, args.tile, args.tile, args.batch),
-            "net": args.net, "batch_per_gpu": args.batch, "tile": args.tile, "img_size": 416,
+def workload_config(args):
+    B = args.batch
+    if args.config == "c5":
+        return {"workload": "C5: NMS stress, %d tiles x 10647 decoded rows x 7, conf_thres 0.01 (every row a candidate), "
+                            "nms_thres 0.4, ay_nms only" % B,
+                "batch_per_gpu": B, "rows": 10647, "classes": 2,
+                "l2": "per step %.0f MB of IoU bit masks + %.0f MB of predictions (L2 is 126 MB)" % (B * 7.1, B * 0.298),
+                "parallelism": "single GPU"}
+    src = "fp32 [B,3,416,416] inputs" if args.config == "c2" else \
+        "synthetic %dx%d uint8 tiles nearest-resized to 416" % (args.tile, args.tile)
+    name = {"c3": "C3/C4", "c1": "C1", "c2": "C2"}[args.config]
+    return {"workload": "%s: %s, %s, batch %d per GPU, conf_thres 0.8, nms_thres 0.4, merge_boxes" % (name, args.net, src, B),
+            "net": args.net, "batch_per_gpu": B, "tile": args.tile, "img_size": 416,
             "checkpoint": "synthetic seed 0 (.pth key layout), conf_bias %s per head, wh_gain 0.15" % args.conf_bias,
-            "l2": "inputs larger than L2 (%.0f MB of tiles, >%.0f MB of activations per step)" % (
-                args.batch * args.tile * args.tile * 3 / 1e6, args.batch * 76.7),
-            "parallelism": "tiles sharded by rank, detections all-gathered" if args.gpus > 1 else "single GPU"}
+            "l2": ("inputs larger than L2 (%.0f MB of tiles, >%.0f MB of activations per step)" % (
+                B * args.tile * args.tile * 3 / 1e6, B * 76.7)) if B >= 8 else
+                  "L2 flushed between timed steps (256 MB scratch write)",
+            "parallelism": "tiles sharded by rank through sweep.sweep, detections all-gathered once per sweep"
+                           if args.gpus > 1 else "single GPU"}
 
 
-# ----------------------------------------------------------------------------- GPU arm
+def emit(args, line, cpu_tiles=None):
+    if not args.no_cpu_baseline:
+        n = args.cpu_sample or cpu_tiles or CONFIGS[args.config]["cpu_tiles"]
+        r = run_cpu_baseline(args, 1, 1, n)
+        line["cpu_baseline"] = {"value": r["tiles_per_s"], "unit": "tiles/s", "cores": r["cores"], "kind": r["kind"],
+                                "sample": "%s, %.1f s, torch %s CPU" % (r["what"], r["seconds"], r["torch"])}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- GPU arm: c5 (NMS only)
+def nms_arm(args):
+    import numpy as np
+    import torch
+    from amyloid_yolo_paper_b200 import _lib, synth
+    from amyloid_yolo_paper_b200.utils.utils import non_max_suppression_device
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    B, K, W = args.batch, max(1, args.steps), max(3, args.warmup)
+    base = synth.synthetic_predictions(min(B, 16), seed=5)
+    P = np.concatenate([base] * (-(-B // len(base))), 0)[:B]
+    N, cols = P.shape[1], P.shape[2]
+    pred0 = torch.from_numpy(P).to(dev)
+    pred = torch.empty_like(pred0)
+    host = torch.from_numpy(P).pin_memory()
+    lib, ctx = _lib.load(), _lib.context(0)
+    stream = torch.cuda.current_stream(dev)
+    st = ctypes.c_void_p(stream.cuda_stream)
+    cap = N
+    rows = torch.empty((B, cap, 7), dtype=torch.float32, device=dev)
+    keep = torch.empty((B, cap), dtype=torch.int32, device=dev)
+    counts = torch.empty((B,), dtype=torch.int32, device=dev)
+
+    def step():
+        pred.copy_(pred0)                   # ay_nms rewrites columns 0..3 in place (utils.py:244): fresh input every step
+        _lib.check(lib.ay_nms(ctx, ctypes.c_void_p(pred.data_ptr()), B, N, cols - 5, 0.01, 0.4, ctypes.c_void_p(rows.data_ptr()),
+                              ctypes.c_void_p(keep.data_ptr()), ctypes.c_void_p(counts.data_ptr()), cap, st))
+
+    for _ in range(W):
+        step()
+    _lib.check(lib.ay_check(ctx, st))
+    clocks = ClockSampler(0)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    e0.record(stream)
+    for _ in range(K):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    _lib.check(lib.ay_check(ctx, st))
+    ms = e0.elapsed_time(e1)
+    kept = int(counts.sum().item())
+    # per-kernel times (events between the four kernels of one call)
+    ms4 = (ctypes.c_float * 4)()
+    parts = [0.0] * 4
+    for _ in range(K):
+        pred.copy_(pred0)
+        _lib.check(lib.ay_nms_timed(ctx, ctypes.c_void_p(pred.data_ptr()), B, N, cols - 5, 0.01, 0.4,
+                                    ctypes.c_void_p(rows.data_ptr()), ctypes.c_void_p(keep.data_ptr()),
+                                    ctypes.c_void_p(counts.data_ptr()), cap, st, ms4))
+        parts = [a + b for a, b in zip(parts, ms4)]
+    parts = [v / K for v in parts]
+    # e2e: pinned host predictions in, kept rows + keep indices + counts out
+    e2e_s = d2h = None
+    if not args.no_e2e:
+        rows_h = torch.empty((B, cap, 7), dtype=torch.float32).pin_memory()
+        keep_h = torch.empty((B, cap), dtype=torch.int32).pin_memory()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for _ in range(K):
+            pred.copy_(host, non_blocking=True)
+            r, k, c = non_max_suppression_device(pred, 0.01, 0.4, cap=cap)
+            c_h = c.cpu()
+            kmax = int(c_h.max())
+            rows_h[:, :kmax].copy_(r[:, :kmax], non_blocking=True)
+            keep_h[:, :kmax].copy_(k[:, :kmax], non_blocking=True)
+            torch.cuda.synchronize(dev)
+            d2h = B * 4 + B * kmax * 32
+        e2e_s = time.perf_counter() - t0
+    clk = clocks.stop()
+    peaks = measured_peaks()
+    mask_bytes = (N * N // 16)                            # upper triangle of the n x n same-class IoU bit matrix
+    algo = B * (N * 20 + mask_bytes)                      # sorted boxes + classes in (20 B per candidate), bit rows out
+    achieved = algo / (parts[1] * 1e-3) / 1e9
+    line = {"metric": METRIC, "value": B * K / (ms * 1e-3), "unit": "tiles/s", "n_gpus": 1, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(args),
+            "gpu_launches": 4 * K,
+            "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"], "samples": clk["samples"]},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s", "frac": achieved / peaks["hbm"],
+                         "traffic": None, "kernel": "nms_mask_kernel (IoU > thres bit matrix, 64x64 blocks)",
+                         "ms": parts[1], "algorithmic_bytes_per_launch": algo, "peak_source": peaks["source"] + " (hbm_gbs)",
+                         "kernels_ms": {"prepare": parts[0], "mask": parts[1], "sweep": parts[2], "cluster": parts[3]}},
+            "kept_per_tile": kept / B}
+    if e2e_s is not None:
+        line["e2e"] = {"value": B * K / e2e_s, "unit": "tiles/s", "h2d_bytes_per_step": int(host.numel() * 4),
+                       "d2h_bytes_per_step": int(d2h), "input": "pinned fp32 [B,10647,7] decoded predictions",
+                       "call": "non_max_suppression_device + read-back of counts, kept rows and keep indices"}
+    emit(args, line)
+
+
+# ----------------------------------------------------------------------------- GPU arm: c1 / c2 / c3
 def main():
     args = parse_args()
     if args.impl == "reference":
         return reference_arm(args)
+    if args.config == "c5":
+        return nms_arm(args)
 
     import torch
     import torch.distributed as dist
-    from amyloid_yolo_paper_b200 import _lib
+    from amyloid_yolo_paper_b200 import _lib, sweep
     from amyloid_yolo_paper_b200.pipeline import TileDetector
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -269,114 +447,206 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     B, K, W = args.batch, max(1, args.steps), max(3, args.warmup)
+    S = 416
+    orig = (S, S) if args.config == "c2" else (args.tile, args.tile)
     cfg, model, sd = build_model(args.net, args.conf_bias)
     cap = 128
     det = TileDetector(model, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=B, cap=cap, device=dev)
-    tiles = device_tiles(B, args.tile, dev, seed=0xA11CE, first_tile=rank * B)
+    float_in = args.config == "c2"
+    if float_in:
+        g = torch.Generator(device=dev).manual_seed(1000 + rank)
+        tiles = torch.rand((B, 3, S, S), device=dev, generator=g)
+        in_kind, sh, sw = _lib.AY_IN_F32_NCHW, S, S
+    else:
+        tiles = device_tiles(B, args.tile, dev, seed=0xA11CE, first_tile=rank * B)
+        in_kind, sh, sw = _lib.AY_IN_U8_HWC, args.tile, args.tile
     torch.cuda.synchronize(dev)
     stream = torch.cuda.current_stream(dev)
-
-    gather_rows = gather_counts = None
-    if world > 1:
-        gather_rows = torch.empty((world * B, cap, 7), dtype=torch.float32, device=dev)
-        gather_counts = torch.empty((world * B,), dtype=torch.int32, device=dev)
-
-    def step():
-        rows, counts = det.run_device(tiles, (args.tile, args.tile))
-        if world > 1:      # config C4: only the per-tile detection lists cross NVLink
-            dist.all_gather_into_tensor(gather_counts, counts)
-            dist.all_gather_into_tensor(gather_rows, rows)
-        return rows, counts
+    flush = torch.empty((256 << 20,), dtype=torch.uint8, device=dev) if B < 8 else None
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    for _ in range(W):
-        step()
+    # ---- value: device-resident inputs through sweep.sweep (the shipped C4 path: shard by rank, run, gather once)
+    def resident(lo, hi):                     # this rank's tiles of a pass: the same B resident tiles every pass
+        return tiles[:hi - lo]
+
+    def run_sweep(steps):
+        if B >= 8:
+            rows, counts = sweep.sweep(det, resident, world * B * steps, B)
+            return rows, counts
+        for _ in range(steps):                # B < 8 (c1): one tile per step, L2 flushed between steps
+            flush.zero_()
+            r, c = det.run_device(tiles, orig)
+        return r, c
+
+    run_sweep(W)
     det.check()
     launches_per_step = det.launches_per_batch
-
-    # ---- value: device-resident inputs, CUDA events on the launching stream
-    fwd_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clocks = ClockSampler(local)
     barrier()
     clocks.start()
-    e0.record(stream)
-    for k in range(K):
-        rows, counts = step()
-    e1.record(stream)
-    barrier()
+    if B >= 8:
+        e0.record(stream)
+        rows, counts = run_sweep(K)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+    else:
+        # single-tile latency: time every step on its own so that the L2 flush stays outside the sum
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        for a, b in evs:
+            flush.zero_()
+            a.record(stream)
+            rows, counts = det.run_device(tiles, orig)
+            b.record(stream)
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
     det.check()
-    ms = e0.elapsed_time(e1)
-    n_det = int(counts.clamp(min=0).sum().item())
+    n_det = int(counts.clamp(min=0).sum().item()) // (world * K if B >= 8 else 1)
 
     # ---- conv stack alone (roofline numerator): events around ay_forward, same inputs, same stream
-    import ctypes
-    fwd_ms = []
-    for k in range(K):
-        a, b = fwd_ev[k]
+    fwd_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for a, b in fwd_ev:
+        if flush is not None:
+            flush.zero_()
         a.record(stream)
-        _lib.check(det.lib.ay_forward(det.ctx, ctypes.c_void_p(tiles.data_ptr()), _lib.AY_IN_U8_HWC, B, args.tile,
-                                      args.tile, ctypes.c_void_p(det.decoded.data_ptr()),
-                                      ctypes.c_void_p(stream.cuda_stream)))
+        _lib.check(det.lib.ay_forward(det.ctx, ctypes.c_void_p(tiles.data_ptr()), in_kind, B, sh, sw,
+                                      ctypes.c_void_p(det.decoded.data_ptr()), ctypes.c_void_p(stream.cuda_stream)))
         b.record(stream)
     torch.cuda.synchronize(dev)
-    fwd_ms = [a.elapsed_time(b) for a, b in fwd_ev]
-    fwd_mean = sum(fwd_ms) / len(fwd_ms)
+    fwd_mean = sum(a.elapsed_time(b) for a, b in fwd_ev) / K
     fwd_launches = det.engine.launch_count()
 
-    # ---- e2e: host buffers through the reference-facing call, copies inside the timed region
-    # the same tiles as the device-resident arm, preprocessed as detect.py's loader does (ToTensor + nearest Resize)
-    x_host = torch.empty((B, 3, 416, 416), dtype=torch.float32).pin_memory()
-    idx = torch.clamp(torch.floor(torch.arange(416, device=dev, dtype=torch.float32) * (float(args.tile) / 416.0)).long(),
-                      max=args.tile - 1)
-    x_host.copy_((tiles[:, idx][:, :, idx].permute(0, 3, 1, 2).float() / 255.0))
-    for _ in range(2):
-        det.detect(x_host, (args.tile, args.tile))
-    # (a) one synchronous detect() per step, as a single-batch caller sees it
-    barrier()
-    t0 = time.perf_counter()
-    for k in range(K):
-        det.detect(x_host, (args.tile, args.tile))
-    barrier()
-    e2e_sync_s = time.perf_counter() - t0
-    # (b) the streaming call a batch loop makes (detect.py:88 iterates a DataLoader): K host batches through
-    # detect_stream; every step's input is copied H2D and its detections D2H inside the timed region, the copies of
-    # step k+1 / k-1 overlap the compute of step k
-    barrier()
-    t0 = time.perf_counter()
-    d2h = 0
-    n_out = 0
-    for outs in det.detect_stream((x_host for _ in range(K)), (args.tile, args.tile)):
-        n_out += len(outs)
-    d2h = det.d2h_bytes                       # bytes actually copied device -> host (counts + padded detection rows)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    assert n_out == K * B
-    clk = clocks.stop()          # sampled over the three timed regions (value, conv stack, e2e): all of them are under load
+    # ---- gather check (N > 1): what arrives on rank 0 for rank r's tiles equals a single-GPU run of the same tile ids
+    gather_verified = None
+    if world > 1:
+        def by_id(lo, hi):
+            return device_tiles(hi - lo, args.tile, dev, seed=0xA11CE, first_tile=lo)
+        all_rows, all_counts = sweep.sweep(det, by_id, world * B, B)
+        ok = True
+        if rank == 0:
+            kk = all_rows.shape[1]
+            col = torch.arange(kk, device=dev).view(1, -1, 1)
+            zero = torch.zeros((), dtype=torch.int32, device=dev)
+            for r in range(world):
+                mine, mc = det.run_device(by_id(r * B, (r + 1) * B))
+                got_r, got_c = all_rows[r * B:(r + 1) * B], all_counts[r * B:(r + 1) * B]
+                ok = ok and torch.equal(got_c, mc) and int(mc.max()) <= kk
+                valid = col < mc.view(-1, 1, 1)
+                ok = ok and torch.equal(torch.where(valid, got_r.view(torch.int32), zero),
+                                        torch.where(valid, mine[:, :kk].contiguous().view(torch.int32), zero))
+                ok = ok and not bool(torch.where(valid, zero, got_r.view(torch.int32)).any())     # padding rows are zero
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.broadcast(flag, 0)
+        gather_verified = bool(flag.item())
+        barrier()
+
+    # ---- e2e: host buffers through the reference-facing calls, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        if float_in:
+            x_host = tiles.cpu().pin_memory()
+            u8_host = None
+        else:
+            # what the loader hands over: the 416^2 source pixels the nearest resize samples (utils/transforms.py:104-111),
+            # gathered on the host into pinned uint8 [B,416,416,3] (0.5 MB per tile); and, for comparison, the fp32
+            # [B,3,416,416] tensor detect.py:94 hands to Darknet.forward (2 MB per tile)
+            idx = torch.clamp(torch.floor(torch.arange(S, device=dev, dtype=torch.float32) * (float(args.tile) / S)).long(),
+                              max=args.tile - 1)
+            small = tiles[:, idx][:, :, idx].contiguous()
+            u8_host = small.cpu().pin_memory()
+            x_host = (small.permute(0, 3, 1, 2).float() / 255.0).cpu().pin_memory()
+
+        def stream_rate(batch_host):
+            for _ in range(2):
+                det.detect(batch_host, orig)
+            barrier()
+            t0 = time.perf_counter()
+            n_out = 0
+            per_tile = []
+            for outs in det.detect_stream((batch_host for _ in range(K)), orig):
+                n_out += len(outs)
+                per_tile.extend(outs)
+            if world > 1:                     # C4: the sweep's single exchange, on the detections of all K batches
+                r_, c_ = sweep.pack_detections(per_tile, device=dev)
+                sweep.allgather_detections(r_, c_, world * B * K)
+            barrier()
+            dt = time.perf_counter() - t0
+            assert n_out == K * B
+            return dt, det.d2h_bytes // K
+
+        def sync_rate(batch_host):
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(K):
+                det.detect(batch_host, orig)
+            barrier()
+            return time.perf_counter() - t0
+
+        main_host = x_host if float_in else u8_host
+        e2e_s, d2h = stream_rate(main_host)
+        e2e = {"unit": "tiles/s", "h2d_bytes_per_step": int(main_host.numel() * main_host.element_size()),
+               "d2h_bytes_per_step": int(d2h),
+               "input": "pinned fp32 [B,3,416,416]" if float_in else
+                        "pinned uint8 [B,416,416,3]: the source pixels the nearest resize samples, gathered by the loader",
+               "call": "TileDetector.detect_stream over the K host batches (one H2D / compute / D2H pipeline across steps)"}
+        times = [e2e_s, sync_rate(main_host)]
+        if not float_in:
+            f32_s, _ = stream_rate(x_host)
+            times.append(f32_s)
+        if args.config == "c1":
+            # the import-swap API of INTEGRATION.md §1, as detect.py:94-133 calls it: model(x) returns the decoded tensor on
+            # the CPU, non_max_suppression / rescale_boxes / mergeDetections take and return CPU tensors
+            from amyloid_yolo_paper_b200.core import mergeDetections
+            from amyloid_yolo_paper_b200.utils.utils import non_max_suppression, rescale_boxes
+            xs = x_host[:1]
+
+            def swap_call():
+                dec = model(xs)
+                dets = non_max_suppression(dec, 0.8, 0.4)
+                for d in dets:
+                    if d is not None:
+                        mergeDetections(rescale_boxes(d, S, orig))
+            for _ in range(3):
+                swap_call()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(K):
+                swap_call()
+            barrier()
+            times.append(time.perf_counter() - t0)
+        if world > 1:
+            t = torch.tensor(times, dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            times = [float(v) for v in t.tolist()]
+        e2e["value"] = world * B * K / times[0]
+        e2e["per_call_sync"] = world * B * K / times[1]
+        if not float_in:
+            e2e["fp32_nchw_input"] = {"value": world * B * K / times[2], "h2d_bytes_per_step": int(x_host.numel() * 4)}
+        if args.config == "c1":
+            e2e["import_swap_api"] = {"value": K / times[-1], "ms_per_tile": 1000.0 * times[-1] / K,
+                                      "call": "Darknet.forward (CPU tensor in, decoded CPU tensor out) + non_max_suppression + "
+                                              "rescale_boxes + mergeDetections"}
+    clk = clocks.stop()          # sampled over all timed regions: every one of them is under load
 
     if world > 1:
-        t = torch.tensor([ms, e2e_s, fwd_mean, e2e_sync_s], dtype=torch.float64, device=dev)
+        t = torch.tensor([ms, fwd_mean], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_s, fwd_mean, e2e_sync_s = (float(v) for v in t.tolist())
+        ms, fwd_mean = (float(v) for v in t.tolist())
 
     if rank == 0:
         peaks = measured_peaks()
         flop = FLOP_PER_TILE[args.net]
         achieved = B * flop / (fwd_mean * 1e-3) / 1e12
-        traffic, traffic_src = profiled_traffic(B)
+        traffic, traffic_src = profiled_traffic(B) if args.config == "c3" else (None, None)
         line = {
             "metric": METRIC, "value": world * B * K / (ms * 1e-3), "unit": "tiles/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic", "config": workload_config(args),
-            "e2e": {"value": world * B * K / e2e_s, "unit": "tiles/s",
-                    "h2d_bytes_per_step": int(x_host.numel() * 4), "d2h_bytes_per_step": int(d2h // K),
-                    "input": "pinned fp32 [B,3,416,416] (the tensor detect.py:94 hands to Darknet.forward)",
-                    "call": "TileDetector.detect_stream over the K host batches (one pipeline across steps)",
-                    "per_call_sync": world * B * K / e2e_sync_s},
             "gpu_launches": int(launches_per_step * K),
             "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
                        "samples": clk["samples"]},
@@ -384,16 +654,15 @@ def main():
                          "frac": achieved / peaks["bf16"], "traffic": traffic, "traffic_unit": "DRAM bytes per ay_forward",
                          "traffic_source": traffic_src,
                          "kernel": "conv stack (ay_forward: %d launches, tcgen05 implicit GEMM)" % fwd_launches,
-                         "ms": fwd_mean, "flop_per_tile": flop, "peak_source": peaks["source"],
+                         "ms": fwd_mean, "flop_per_tile": flop, "peak_source": peaks["source"] + " (sustained bf16)",
                          "frac_of_burst": achieved / peaks["bf16_burst"]},
-            "detections_last_step": n_det,
+            "detections_per_step": n_det,
         }
-        if not args.no_cpu_baseline:
-            r = run_cpu_baseline(args, 1, 1)
-            line["cpu_baseline"] = {"value": r["tiles_per_s"], "unit": "tiles/s", "cores": r["cores"], "kind": "port",
-                                    "sample": "%d fp32 [3,416,416] tiles, forward+NMS+rescale+mergeDetections "
-                                              "(oracle port of the reference path), %.1f s" % (r["tiles"], r["seconds"])}
-        print(json.dumps(line), flush=True)
+        if e2e is not None:
+            line["e2e"] = e2e
+        if gather_verified is not None:
+            line["gather_verified"] = gather_verified
+        emit(args, line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

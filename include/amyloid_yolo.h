@@ -103,6 +103,12 @@ int  ay_net_launch_count(ay_ctx* ctx);
 int  ay_nms(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes,
             float conf_thres, float nms_thres,
             float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream);
+/* ay_nms with a CUDA event between its four kernels (prepare, mask, sweep, cluster): synchronises `stream` and
+ * writes their milliseconds to ms4_h[4].  Measurement aid of bench.py --config c5.          */
+int  ay_nms_timed(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes,
+                  float conf_thres, float nms_thres,
+                  float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream,
+                  float* ms4_h);
 /* utils/utils.py:36-50 followed (merge != 0) by core.py:366-423, per tile.
  * rows [B,cap,7] / counts [B] as produced by ay_nms; results in out_rows [B,cap,7]
  * (row order = the reference's CPython-3.12 set order) and out_counts [B].          */

@@ -41,8 +41,20 @@ class _Inert(types.ModuleType):
         return _Inert(self.__name__ + "()")
 
 
-def available():
+ARCHIVE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "reference_py.zip")
+
+
+def checkout_available():
     return os.path.isfile(os.path.join(REFERENCE_ROOT, "models.py"))
+
+
+def available():
+    """The mounted checkout (build container) or the archive ``oracle/build_ref.py`` packed from it (GPU box)."""
+    return checkout_available() or os.path.isfile(ARCHIVE)
+
+
+def source():
+    return "checkout" if checkout_available() else ("archive" if os.path.isfile(ARCHIVE) else None)
 
 
 _cache = {}
@@ -53,7 +65,8 @@ def load():
     if "mods" in _cache:
         return _cache["mods"]
     if not available():
-        raise RuntimeError("reference checkout not found at %s" % REFERENCE_ROOT)
+        raise RuntimeError("reference sources not found (%s, %s)" % (REFERENCE_ROOT, ARCHIVE))
+    root = REFERENCE_ROOT if checkout_available() else ARCHIVE        # zipimport handles the archive
     for name in _ABSENT:
         try:
             importlib.import_module(name)
@@ -65,16 +78,17 @@ def load():
     # ours do not shadow them and vice versa.
     saved = {k: sys.modules.pop(k) for k in list(sys.modules)
              if k in ("utils", "models", "core") or k.startswith("utils.")}
-    sys.path.insert(0, REFERENCE_ROOT)
+    sys.path.insert(0, root)
     cwd = os.getcwd()
     try:
-        os.chdir(REFERENCE_ROOT)
+        if os.path.isdir(root):
+            os.chdir(root)
         models = importlib.import_module("models")
         uu = importlib.import_module("utils.utils")
         core = importlib.import_module("core")
     finally:
         os.chdir(cwd)
-        sys.path.remove(REFERENCE_ROOT)
+        sys.path.remove(root)
     ref = {k: sys.modules.pop(k) for k in list(sys.modules)
            if k in ("utils", "models", "core") or k.startswith("utils.")}
     _cache["ref_modules"] = ref

@@ -280,3 +280,46 @@ def test_several_contexts_in_one_process(dev):
         assert len(ra) == 2 and len(rb) == 2
         out, keep = non_max_suppression(torch.from_numpy(P.copy()).to(d), 0.3, 0.4, return_keep=True)
         assert np.array_equal(keep[0].numpy(), want_keep) and np.array_equal(bits(out[0]), bits(want_rows))
+
+
+# ------------------------------------------------------------------ real-image ingest and the CLI
+def test_detect_cli_on_jpeg_tiles(dev, tmp_path):
+    """detect.run over a folder of JPEG tiles written here (the GPU box has no reference checkout): PIL decode in
+    worker threads, pre-gathered pinned uint8 [b,416,416,3] upload, --batch_size / --n_cpu honoured.  The detections
+    equal the oracle's post-processing of the decoded tensor the engine produces from the FULL 1536^2 tiles (so the
+    host-side gather is checked against the in-kernel resize as well), and the forward meets the raw-head bar."""
+    from PIL import Image
+    from amyloid_yolo_paper_b200 import detect, synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    cfg = ensure_cfg("yolov3-custom")
+    m, sd = _model(cfg, seed=1, conf_bias=(-6.0, -1.5, -6.0), wh_gain=0.15)
+    torch.save(sd, str(tmp_path / "ckpt.pth"))
+    folder = tmp_path / "tiles"
+    folder.mkdir()
+    raw = synth.synthetic_tiles(5, size=1536, seed=13)
+    for i, t in enumerate(raw):
+        Image.fromarray(t).save(str(folder / ("tile_%02d.jpg" % i)), quality=90)
+    (tmp_path / "classes.names").write_text("CAA\nCored\n")
+    opt = detect.build_parser().parse_args([
+        "--image_folder", str(folder), "--model_def", cfg, "--weights_path", str(tmp_path / "ckpt.pth"),
+        "--class_path", str(tmp_path / "classes.names"), "--conf_thres", "0.8", "--nms_thres", "0.4", "--img_size", "416",
+        "--batch_size", "2", "--n_cpu", "2", "--merge_boxes", "True", "--output", str(tmp_path / "out")])
+    results = detect.run(opt)
+    files = sorted(str(p) for p in folder.iterdir())
+    assert list(results) == files and (tmp_path / "out" / "detections.json").exists()
+    decoded_imgs = np.stack([detect.load_image(f) for f in files])
+    eng = m.engine(device=dev, max_batch=5)
+    dec = eng.forward_u8(torch.from_numpy(decoded_imgs)).cpu()
+    eng.check()
+    blocks = R.parse_cfg(cfg)
+    x = torch.stack([R.preprocess_u8(t, 416) for t in decoded_imgs])
+    with torch.no_grad():
+        _, raw32 = R.darknet_forward(blocks, sd, x, return_raw_heads=True)
+    assert raw_head_error(dec, raw32, blocks) <= 2e-2
+    n = 0
+    for b, f in enumerate(files):
+        want = _oracle_final(dec[b].numpy())
+        got = np.asarray(results[f], dtype=np.float32).reshape(-1, 7)
+        assert got.shape == want.shape and np.array_equal(bits(got), bits(want)), f
+        n += len(want)
+    assert n > 0

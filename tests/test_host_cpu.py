@@ -196,3 +196,36 @@ def test_shard_ranges_cover_all_tiles():
             assert spans[0][0] == 0 and spans[-1][1] == n
             assert all(spans[i][1] == spans[i + 1][0] for i in range(w - 1))
             assert max(b - a for a, b in spans) - min(b - a for a, b in spans) <= 1
+
+
+def test_loader_gather_equals_reference_transform_chain(tmp_path):
+    """utils/datasets.py: gathering the sampled pixels on the uint8 image == PadSquare -> ToTensor -> Resize of the
+    reference (utils/transforms.py:80-111) element for element, for square tiles and for both kinds of padding."""
+    import torch.nn.functional as F
+    from PIL import Image
+    from amyloid_yolo_paper_b200.detect import pad_square
+    from amyloid_yolo_paper_b200.utils.datasets import ImageFolder, TileLoader, gather_resized, nearest_index
+    from oracle import restate as R
+    rng = np.random.default_rng(0)
+    for (h, w), S in (((1536, 1536), 416), ((300, 200), 64), ((201, 300), 96), ((50, 50), 64), ((640, 640), 320)):
+        img = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+        sq = pad_square(img)
+        x = torch.from_numpy(np.ascontiguousarray(sq)).permute(2, 0, 1).to(torch.float32).div(255)      # ToTensor
+        want = F.interpolate(x.unsqueeze(0), size=S, mode="nearest").squeeze(0)                           # Resize
+        got = torch.from_numpy(gather_resized(img, S)).permute(2, 0, 1).to(torch.float32).div(255)
+        assert torch.equal(got, want), (h, w, S)
+        assert np.array_equal(nearest_index(S, max(h, w)), R.nearest_src_index(S, max(h, w)))
+    # the loader: sorted file order, batches of one original shape, pinned-or-not uint8 blocks
+    shapes = [(40, 40), (40, 40), (40, 40), (30, 50), (40, 40)]
+    imgs = []
+    for i, (h, w) in enumerate(shapes):
+        a = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+        imgs.append(a)
+        Image.fromarray(a).save(str(tmp_path / ("t%02d.png" % i)))
+    ds = ImageFolder(str(tmp_path), img_size=32)
+    assert len(ds) == 5 and ds[3][2] == (30, 50) and ds[0][1].dtype == torch.uint8 and tuple(ds[0][1].shape) == (32, 32, 3)
+    got = [(list(p), t.clone(), s) for p, t, s in TileLoader(str(tmp_path), img_size=32, batch_size=2, n_cpu=3)]
+    assert [len(g[0]) for g in got] == [2, 1, 1, 1] and [g[2] for g in got] == [(40, 40), (40, 40), (30, 50), (40, 40)]
+    flat = [t for g in got for t in g[1]]
+    for a, t in zip(imgs, flat):
+        assert np.array_equal(t.numpy(), gather_resized(a, 32))
