@@ -87,6 +87,11 @@ struct ConvGemmParams {
   int dec_rows_total, dec_row_off, dec_cols, n_anchors, cout;
   float stride;
   float anchor_w[8], anchor_h[8];   // already divided by stride (models.py:122)
+  // confidence-threshold compaction (heads; nullptr = off): rows with conf >= conf_thres are appended to the tile's list
+  int32_t* cand_idx;     // [B, cand_cap] decoded row indices, arbitrary order
+  int32_t* cand_count;   // [B], zeroed by the caller before the forward; counts past cand_cap mean "list incomplete"
+  int cand_cap;
+  float conf_thres;
   unsigned int* err_flag;
   unsigned long long* prof;   // kProfWords counters (profiling runs only), else nullptr: [0..15] cycle counters of CTA 0,
                               // then %globaltimer stamps of every CTA: entry, end of prologue, exit, dependency resolved
@@ -172,7 +177,8 @@ struct NmsScratch {
 size_t nms_scratch_bytes(int batch, int n_rows);
 int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres,
                float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap,
-               void* scratch, size_t scratch_bytes, unsigned int* err_flag, cudaStream_t s, cudaEvent_t* ev = nullptr);
+               void* scratch, size_t scratch_bytes, unsigned int* err_flag, cudaStream_t s, cudaEvent_t* ev = nullptr,
+               const int32_t* cand_idx = nullptr, const int32_t* cand_count = nullptr, int cand_cap = 0);
 size_t merge_scratch_bytes(int batch, int cap);
 int launch_rescale_merge(const float* rows, const int32_t* counts, int batch, int cap,
                          float pad_x_half, float pad_y_half, float unpad_w, float unpad_h,

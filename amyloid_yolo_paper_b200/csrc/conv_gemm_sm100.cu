@@ -217,6 +217,30 @@ __device__ __forceinline__ void stg256(void* ptr, const uint32_t* v) {
                ::"l"(ptr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
                : "memory");
 }
+// Confidence-threshold compaction fused into the head epilogue (utils/utils.py:248: image_pred[image_pred[:, 4] >=
+// conf_thres]): the decoded row index of every passing row is appended to its tile's candidate list.  One atomic per
+// warp and anchor when the warp's rows belong to one image (always, except across an image boundary); the order of
+// the list is arbitrary - NMS sorts candidates by (score, row) before anything depends on it.  Counts beyond cand_cap
+// are still counted, so the consumer sees the overflow and falls back to scanning the dense tensor for that tile.
+__device__ __forceinline__ void append_candidates(const ConvGemmParams& p, bool pass, bool one_image, int img,
+                                                  int img_first, int row, int lane) {
+  if (one_image) {
+    const unsigned m = __ballot_sync(0xffffffffu, pass);
+    if (m == 0u) return;
+    int base = 0;
+    const int leader = __ffs(m) - 1;
+    if (lane == leader) base = atomicAdd(p.cand_count + img_first, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pass) {
+      const int slot = base + __popc(m & ((1u << lane) - 1u));
+      if (slot < p.cand_cap) p.cand_idx[(size_t)img_first * p.cand_cap + slot] = row;
+    }
+  } else if (pass) {
+    const int slot = atomicAdd(p.cand_count + img, 1);
+    if (slot < p.cand_cap) p.cand_idx[(size_t)img * p.cand_cap + slot] = row;
+  }
+}
+
 // G = taps per pipeline stage (3: the kw taps of one kh share one 130-row A box; 1: one tap per stage)
 template <int G, bool FP16, bool SPLIT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
@@ -713,6 +737,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
               for (int f = 0; f < 7; ++f) dst[f] = r[f];
             }
+            if (p.cand_count != nullptr)
+              append_candidates(p, valid && r[4] >= p.conf_thres, one_image, img, img_first,
+                                p.dec_row_off + a * Gd * Gd + gy * Gd + gx, lane);
           }
         } else
         for (int c = c_first; c < nchunks; c += c_step) {
@@ -735,6 +762,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const float off = (fj == 0) ? (float)gx : (float)gy;
             const float box = wh ? __fmul_rn(__fmul_rn(e, anchor), p.stride) : __fmul_rn(__fadd_rn(sg, off), p.stride);
             r[j] = (fj < 4) ? box : sg;
+            // objectness channel: rows that clear the confidence threshold are appended to the tile's candidate list
+            // (utils/utils.py:248 `>=` on the fp32 value that is stored)
+            if (p.cand_count != nullptr && fj == 4 && valid && sg >= p.conf_thres) {
+              const int slot = atomicAdd(p.cand_count + img, 1);
+              if (slot < p.cand_cap) p.cand_idx[(size_t)img * p.cand_cap + slot] = p.dec_row_off + aj * Gd * Gd + gy * Gd + gx;
+            }
             if (++fj == p.dec_cols) { fj = 0; aj = min(aj + 1, p.n_anchors - 1); }
           }
           int a = ch0 / p.dec_cols, fi = ch0 - a * p.dec_cols;   // running (anchor, field) of channel ch

@@ -169,6 +169,8 @@ struct ay_ctx {
   int launches = 0;
   // per-layer timing (ay_forward_profile): one event before every cfg block and one after the last
   bool profiling = false;
+  // ay_forward_candidates: where the head epilogues append the rows that clear the confidence threshold (one forward)
+  int32_t* cand_idx = nullptr; int32_t* cand_count = nullptr; int cand_cap = 0; float cand_thres = 0.f;
   bool stamping = false;              // ay_forward_stamps: per-CTA %globaltimer stamps, no events between the launches
   std::vector<cudaEvent_t> prof_events;
   unsigned long long* prof_counters = nullptr;   // [n_layers][16], device
@@ -955,6 +957,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   if (L.is_head) {
     q.head = 1;
     q.head_stage_bytes = L.head_stage_bytes;
+    q.cand_idx = ctx->cand_idx; q.cand_count = ctx->cand_count; q.cand_cap = ctx->cand_cap; q.conf_thres = ctx->cand_thres;
     q.head_fast = (ctx->dec_cols == 7 && Y->d.n_anchors == 3 && L.C == 21 && L.BN == 32 && L.cout_rows == 32 &&
                    L.m_batch == 1 && !ctx->no_head_fast) ? 1 : 0;
     q.dec_out = dec_out; q.dec_rows_total = ctx->dec_rows; q.dec_row_off = Y->dec_row_off;
@@ -1069,6 +1072,49 @@ extern "C" int ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch
   return AY_OK;
 }
 
+static int ensure_scratch(void** buf, size_t* have, size_t need) {
+  if (*have >= need) return AY_OK;
+  AY_CUDA(cudaDeviceSynchronize());
+  if (*buf) cudaFree(*buf);
+  *buf = nullptr;
+  *have = 0;
+  cudaError_t e = cudaMalloc(buf, need);
+  if (e != cudaSuccess) { set_error("cudaMalloc(%zu bytes of scratch) failed: %s", need, cudaGetErrorString(e)); return AY_ENOMEM; }
+  *have = need;
+  return AY_OK;
+}
+
+extern "C" int ay_forward_candidates(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                                     float* out_decoded, float conf_thres, int32_t* cand_idx, int32_t* cand_count,
+                                     int cand_cap, void* stream) {
+  AY_ENTER(ctx);
+  if (!cand_idx || !cand_count || cand_cap < 1) { set_error("ay_forward_candidates: bad candidate buffers"); return AY_EINVAL; }
+  if (ctx->is_f32 || ctx->use_ref) {
+    set_error("ay_forward_candidates: the compaction is part of the tensor-core head epilogue (bf16 / fp16 networks)");
+    return AY_EINVAL;
+  }
+  if (batch >= 1) AY_CUDA(cudaMemsetAsync(cand_count, 0, sizeof(int32_t) * (size_t)batch, static_cast<cudaStream_t>(stream)));
+  ctx->cand_idx = cand_idx; ctx->cand_count = cand_count; ctx->cand_cap = cand_cap; ctx->cand_thres = conf_thres;
+  const int rc = ay_forward(ctx, input, in_kind, batch, src_h, src_w, out_decoded, stream);
+  ctx->cand_idx = nullptr; ctx->cand_count = nullptr; ctx->cand_cap = 0;
+  if (rc == AY_OK) ++ctx->launches;                       // the memset node
+  return rc;
+}
+
+extern "C" int ay_nms_candidates(ay_ctx* ctx, float* decoded, const int32_t* cand_idx, const int32_t* cand_count,
+                                 int cand_cap, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres,
+                                 float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream) {
+  AY_ENTER(ctx);
+  if (!decoded || !cand_idx || !cand_count || cand_cap < 1 || !out_rows || !out_keep || !out_counts || batch < 1 || n_rows < 1) {
+    set_error("ay_nms_candidates: bad arguments");
+    return AY_EINVAL;
+  }
+  AY_TRY(ensure_scratch(&ctx->nms_scratch, &ctx->nms_bytes, ay::nms_scratch_bytes(batch, n_rows)));
+  return ay::launch_nms(decoded, batch, n_rows, n_classes, conf_thres, nms_thres, out_rows, out_keep, out_counts, cap,
+                        ctx->nms_scratch, ctx->nms_bytes, ctx->err_flag, static_cast<cudaStream_t>(stream), nullptr,
+                        cand_idx, cand_count, cand_cap < n_rows ? cand_cap : n_rows);
+}
+
 extern "C" int ay_debug_set(ay_ctx* ctx, int bits) {
   if (!ctx) { set_error("null context"); return AY_EINVAL; }
   ctx->dbg = bits;
@@ -1159,18 +1205,6 @@ extern "C" int ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out
   }
   return ay::launch_dump_nchw(L.out.ptr, L.out.pitch, L.C, batch, L.H, L.W, ctx->is_fp16, out_nchw,
                               static_cast<cudaStream_t>(stream));
-}
-
-static int ensure_scratch(void** buf, size_t* have, size_t need) {
-  if (*have >= need) return AY_OK;
-  AY_CUDA(cudaDeviceSynchronize());
-  if (*buf) cudaFree(*buf);
-  *buf = nullptr;
-  *have = 0;
-  cudaError_t e = cudaMalloc(buf, need);
-  if (e != cudaSuccess) { set_error("cudaMalloc(%zu bytes of scratch) failed: %s", need, cudaGetErrorString(e)); return AY_ENOMEM; }
-  *have = need;
-  return AY_OK;
 }
 
 extern "C" int ay_nms(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes, float conf_thres,

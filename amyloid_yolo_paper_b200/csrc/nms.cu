@@ -64,8 +64,14 @@ __device__ __forceinline__ float iou_xyxy(const float4 a, const float4 b) {
 }
 
 // ------------------------------------------------------------------ prepare
+// Two entry modes.  Dense (cand_idx == nullptr, the reference-shaped ay_nms): every row is rewritten xywh -> xyxy IN PLACE
+// (utils/utils.py:244 mutates its argument) and filtered by confidence here.  Candidates (ay_nms_candidates): the head
+// convolutions' epilogue has already compacted the rows with conf >= conf_thres into per-tile index lists, the dense
+// tensor is only read at those rows and stays xywh; a tile whose list overflowed (count > cand_cap) is scanned densely
+// instead, without the in-place rewrite.
 __global__ void __launch_bounds__(kSortThreads, 1)
-nms_prepare_kernel(float* __restrict__ pred, int n, int n_classes, float conf_thres, uint8_t* scratch, NmsLayout L) {
+nms_prepare_kernel(float* __restrict__ pred, int n, int n_classes, float conf_thres, uint8_t* scratch, NmsLayout L,
+                   const int32_t* __restrict__ cand_idx, const int32_t* __restrict__ cand_count, int cand_cap) {
   extern __shared__ unsigned long long keys[];   // npow2 entries
   __shared__ int s_count;
   const int b = blockIdx.x;
@@ -73,28 +79,42 @@ nms_prepare_kernel(float* __restrict__ pred, int n, int n_classes, float conf_th
   float* tile = pred + (size_t)b * n * cols;
   if (threadIdx.x == 0) s_count = 0;
   __syncthreads();
+  const bool in_place = cand_idx == nullptr;
+  const int listed = in_place ? -1 : cand_count[b];
+  const bool use_list = listed >= 0 && listed <= cand_cap;
+  auto score_key = [&](const float* row, int r) {
+    float best = row[5];
+    for (int c = 1; c < n_classes; ++c) {
+      const float v = row[5 + c];
+      if (v > best) best = v;
+    }
+    const float score = __fmul_rn(row[4], best);
+    // descending score, ascending row: order-preserving float->uint map, inverted
+    unsigned int u = __float_as_uint(score);
+    u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    return ((unsigned long long)(~u) << 32) | (unsigned int)r;
+  };
+  if (use_list) {
+    for (int i = threadIdx.x; i < listed; i += blockDim.x) {
+      const int r = cand_idx[(size_t)b * cand_cap + i];
+      keys[i] = score_key(tile + (size_t)r * cols, r);
+    }
+    if (threadIdx.x == 0) s_count = listed;
+  } else
   // pass 1: xyxy in place + candidate keys (unordered append; the sort makes it deterministic)
   for (int r = threadIdx.x; r < n; r += blockDim.x) {
     float* row = tile + (size_t)r * cols;
-    const float cx = row[0], cy = row[1], w = row[2], h = row[3];
-    const float hw = __fdiv_rn(w, 2.0f), hh = __fdiv_rn(h, 2.0f);
-    row[0] = __fsub_rn(cx, hw);
-    row[1] = __fsub_rn(cy, hh);
-    row[2] = __fadd_rn(cx, hw);
-    row[3] = __fadd_rn(cy, hh);
-    const float conf = row[4];
-    if (conf >= conf_thres) {
-      float best = row[5];
-      for (int c = 1; c < n_classes; ++c) {
-        const float v = row[5 + c];
-        if (v > best) best = v;
-      }
-      const float score = __fmul_rn(conf, best);
-      // descending score, ascending row: order-preserving float->uint map, inverted
-      unsigned int u = __float_as_uint(score);
-      u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    if (in_place) {
+      const float cx = row[0], cy = row[1], w = row[2], h = row[3];
+      const float hw = __fdiv_rn(w, 2.0f), hh = __fdiv_rn(h, 2.0f);
+      row[0] = __fsub_rn(cx, hw);
+      row[1] = __fsub_rn(cy, hh);
+      row[2] = __fadd_rn(cx, hw);
+      row[3] = __fadd_rn(cy, hh);
+    }
+    if (row[4] >= conf_thres) {
       const int slot = atomicAdd(&s_count, 1);
-      keys[slot] = ((unsigned long long)(~u) << 32) | (unsigned int)r;
+      keys[slot] = score_key(row, r);
     }
   }
   __syncthreads();
@@ -126,7 +146,13 @@ nms_prepare_kernel(float* __restrict__ pred, int n, int n_classes, float conf_th
   for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
     const int r = (int)(keys[i] & 0xFFFFFFFFull);
     const float* row = tile + (size_t)r * cols;
-    box[i] = make_float4(row[0], row[1], row[2], row[3]);
+    if (in_place) {
+      box[i] = make_float4(row[0], row[1], row[2], row[3]);
+    } else {                                             // xywh2xyxy of this candidate only (utils/utils.py:53-59)
+      const float cx = row[0], cy = row[1];
+      const float hw = __fdiv_rn(row[2], 2.0f), hh = __fdiv_rn(row[3], 2.0f);
+      box[i] = make_float4(__fsub_rn(cx, hw), __fsub_rn(cy, hh), __fadd_rn(cx, hw), __fadd_rn(cy, hh));
+    }
     conf[i] = row[4];
     float best = row[5];
     int arg = 0;
@@ -371,7 +397,8 @@ size_t nms_scratch_bytes(int batch, int n_rows) { return make_layout(batch, n_ro
 
 int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres, float* out_rows,
                int32_t* out_keep, int32_t* out_counts, int cap, void* scratch, size_t scratch_bytes,
-               unsigned int* err_flag, cudaStream_t s, cudaEvent_t* ev) {
+               unsigned int* err_flag, cudaStream_t s, cudaEvent_t* ev, const int32_t* cand_idx,
+               const int32_t* cand_count, int cand_cap) {
   if (n_rows > kMaxRows) {
     set_error("nms: %d rows per tile exceed the on-chip sort capacity of %d", n_rows, kMaxRows);
     return AY_EINVAL;
@@ -393,7 +420,8 @@ int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thr
   uint8_t* sc = static_cast<uint8_t*>(scratch);
   // ev (ay_nms_timed only): five events bracketing the four kernels
   if (ev) AY_CUDA(cudaEventRecord(ev[0], s));
-  nms_prepare_kernel<<<batch, kSortThreads, sort_smem, s>>>(pred, n_rows, n_classes, conf_thres, sc, L);
+  nms_prepare_kernel<<<batch, kSortThreads, sort_smem, s>>>(pred, n_rows, n_classes, conf_thres, sc, L, cand_idx, cand_count,
+                                                            cand_cap);
   AY_CUDA(cudaGetLastError());
   if (ev) AY_CUDA(cudaEventRecord(ev[1], s));
   nms_mask_kernel<<<dim3(96, batch), 64, 0, s>>>(n_rows, nms_thres, sc, L);

@@ -58,6 +58,13 @@ class TileDetector:
         self.nms_rows = torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev)
         self.nms_keep = torch.empty((B, self.cap), dtype=torch.int32, device=dev)
         self.nms_counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        # candidate lists filled by the head convolutions' epilogue (conf >= conf_thres, utils/utils.py:248): NMS starts
+        # from these instead of re-reading the dense decoded tensor.  A tile with more candidates than cand_cap is
+        # handled by a dense scan of that tile (never truncated).
+        self.cand_cap = int(min(self.rows, max(1024, 4 * self.cap)))
+        self.cand_idx = torch.empty((B, self.cand_cap), dtype=torch.int32, device=dev)
+        self.cand_count = torch.zeros((B,), dtype=torch.int32, device=dev)
+        self.fuse_threshold = True          # False: ay_forward + ay_nms (dense scan, in-place xyxy) as in round 1
         # two result slots: the host path reads slot i while the device fills slot i+1
         self._out_rows = [torch.empty((B, self.cap, 7), dtype=torch.float32, device=dev) for _ in range(2)]
         self._out_counts = [torch.empty((B,), dtype=torch.int32, device=dev) for _ in range(2)]
@@ -109,10 +116,17 @@ class TileDetector:
         self._bind_engine()
         lib, ctx = self.lib, self.ctx
         with torch.cuda.device(self.device):
-            _lib.check(lib.ay_forward(ctx, _ptr(tiles), kind, B, sh, sw, _ptr(self.decoded), st))
-            _lib.check(lib.ay_nms(ctx, _ptr(self.decoded), B, self.rows, self.cols - 5, self.conf_thres,
-                                  self.nms_thres, _ptr(self.nms_rows), _ptr(self.nms_keep), _ptr(self.nms_counts),
-                                  self.cap, st))
+            if self.fuse_threshold and self.engine.precision != "fp32":
+                _lib.check(lib.ay_forward_candidates(ctx, _ptr(tiles), kind, B, sh, sw, _ptr(self.decoded), self.conf_thres,
+                                                     _ptr(self.cand_idx), _ptr(self.cand_count), self.cand_cap, st))
+                _lib.check(lib.ay_nms_candidates(ctx, _ptr(self.decoded), _ptr(self.cand_idx), _ptr(self.cand_count),
+                                                 self.cand_cap, B, self.rows, self.cols - 5, self.conf_thres, self.nms_thres,
+                                                 _ptr(self.nms_rows), _ptr(self.nms_keep), _ptr(self.nms_counts), self.cap, st))
+            else:
+                _lib.check(lib.ay_forward(ctx, _ptr(tiles), kind, B, sh, sw, _ptr(self.decoded), st))
+                _lib.check(lib.ay_nms(ctx, _ptr(self.decoded), B, self.rows, self.cols - 5, self.conf_thres,
+                                      self.nms_thres, _ptr(self.nms_rows), _ptr(self.nms_keep), _ptr(self.nms_counts),
+                                      self.cap, st))
             _lib.check(lib.ay_rescale_merge(ctx, _ptr(self.nms_rows), _ptr(self.nms_counts), B, self.cap,
                                             self.img_size, int(original_shape[0]), int(original_shape[1]),
                                             1 if self.merge_boxes else 0, _ptr(self._out_rows[slot]),

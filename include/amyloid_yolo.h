@@ -82,6 +82,14 @@ int  ay_net_output_shape(ay_ctx* ctx, int* rows, int* cols);
 /* Forward + YOLO decode.  out_decoded: [B, rows, cols] fp32 (xywh, as models.py:161-169). */
 int  ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
                 float* out_decoded, void* stream);
+/* ay_forward with the confidence threshold of non_max_suppression (utils/utils.py:248, `conf >= conf_thres` on the
+ * fp32 value) fused into the head convolutions' epilogue: besides the dense decoded tensor, the decoded ROW INDEX of
+ * every passing row is appended to its tile's list cand_idx[b, 0..cand_count[b]) (order arbitrary; cand_count is
+ * zeroed here).  cand_count[b] > cand_cap means tile b's list is incomplete - ay_nms_candidates then scans that
+ * tile's dense rows instead.  bf16 / fp16 networks only.                                         */
+int  ay_forward_candidates(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_h, int src_w,
+                           float* out_decoded, float conf_thres,
+                           int32_t* cand_idx, int32_t* cand_count, int cand_cap, void* stream);
 /* Debug/test helper: copy the stored output of layer `layer` (conv, maxpool, upsample,
  * shortcut, route) of the last forward into out_nchw [B,C,H,W] fp32.                */
 int  ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out_nchw, void* stream);
@@ -103,6 +111,12 @@ int  ay_net_launch_count(ay_ctx* ctx);
 int  ay_nms(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes,
             float conf_thres, float nms_thres,
             float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream);
+/* ay_nms starting from the candidate lists of ay_forward_candidates (same conf_thres): only the listed rows of
+ * `decoded` are read, and `decoded` is NOT rewritten to xyxy (it is the pipeline's internal buffer, not a caller's
+ * tensor).  Results are bit-identical to ay_nms on the same decoded tensor.                          */
+int  ay_nms_candidates(ay_ctx* ctx, float* decoded, const int32_t* cand_idx, const int32_t* cand_count, int cand_cap,
+                       int batch, int n_rows, int n_classes, float conf_thres, float nms_thres,
+                       float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream);
 /* ay_nms with a CUDA event between its four kernels (prepare, mask, sweep, cluster): synchronises `stream` and
  * writes their milliseconds to ms4_h[4].  Measurement aid of bench.py --config c5.          */
 int  ay_nms_timed(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes,

@@ -441,6 +441,14 @@ def test_pipeline_end_to_end_vs_oracle_chain(dev):
     tiles = synth.synthetic_tiles(B, size=1536, seed=9)
     det = TileDetector(m, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=B, cap=512, device=dev)
     got = det.detect(torch.from_numpy(tiles))
+    # the fused pipeline starts NMS from the head epilogue's candidate lists and leaves its internal decoded buffer in
+    # xywh; the reference-shaped ay_nms path (fuse_threshold = False) rewrites it to xyxy in place (utils.py:244)
+    assert np.array_equal(bits(det.decoded[:B].cpu()), bits(det.engine.forward_u8(torch.from_numpy(tiles)).cpu()))
+    det.fuse_threshold = False
+    got_dense = det.detect(torch.from_numpy(tiles))
+    det.fuse_threshold = True
+    for a, b in zip(got, got_dense):
+        assert (a is None) == (b is None) and (a is None or torch.equal(a.view(torch.int32), b.view(torch.int32)))
     decoded = det.decoded[:B].cpu().numpy()            # columns 0..3 already xyxy (in-place convention)
     # (1) oracle post-processing on the GPU's decoded tensor (undo xyxy -> feed xyxy through the exact NMS core)
     x = torch.stack([R.preprocess_u8(t, 416) for t in tiles])
