@@ -43,15 +43,15 @@ __global__ void first_conv_kernel(FirstConvParams p) {
   const int nw = p.cout * 27;
   for (int i = threadIdx.x; i < nw + p.cout; i += blockDim.x) sw[i] = (i < nw) ? p.w[i] : p.bias[i - nw];
   __syncthreads();
-  const int Sp = p.S + 2;
+  const int Sp = padded(p.S);
   const long long total = (long long)p.batch * Sp * Sp;
   const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= total) return;
   const int n = (int)(m / ((long long)Sp * Sp));
   const int pix = (int)(m - (long long)n * Sp * Sp);
-  const int y = pix / Sp, x = pix - y * Sp;
+  const int y = pix / Sp - kPadLo, x = pix - (pix / Sp) * Sp - kPadLo;      // unpadded output pixel
   uint16_t* orow = static_cast<uint16_t*>(p.out) + (size_t)m * p.out_pitch;
-  const bool halo = (y == 0) | (y == Sp - 1) | (x == 0) | (x == Sp - 1);
+  const bool halo = (y < 0) | (y >= p.S) | (x < 0) | (x >= p.S);
   if (halo) {
     for (int c = 0; c < p.Cp; c += 8) *reinterpret_cast<uint4*>(orow + c) = make_uint4(0, 0, 0, 0);
     return;
@@ -61,7 +61,7 @@ __global__ void first_conv_kernel(FirstConvParams p) {
   for (int kh = 0; kh < 3; ++kh) {
 #pragma unroll
     for (int kw = 0; kw < 3; ++kw) {
-      const int iy = y - 1 + kh - 1, ix = x - 1 + kw - 1;
+      const int iy = y + kh - 1, ix = x + kw - 1;
       const bool ok = (iy >= 0) & (iy < p.S) & (ix >= 0) & (ix < p.S);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -108,13 +108,13 @@ __global__ void first_conv_kernel(FirstConvParams p) {
 // (3 used) per pixel: 16 bytes per pixel, so that three horizontally adjacent pixels are 24 contiguous
 // elements and one TMA row of the first layer's A operand (see engine.cu, first layer).
 __global__ void prep_input_kernel(FirstConvParams p) {
-  const int Sp = p.S + 2;
+  const int Sp = padded(p.S);
   const long long total = (long long)p.batch * Sp * Sp;
   const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= total) return;
   const int n = (int)(m / ((long long)Sp * Sp));
   const int pix = (int)(m - (long long)n * Sp * Sp);
-  const int y = pix / Sp - 1, x = pix - (pix / Sp) * Sp - 1;
+  const int y = pix / Sp - kPadLo, x = pix - (pix / Sp) * Sp - kPadLo;
   float v[3] = {0.f, 0.f, 0.f};
   if (y >= 0 && y < p.S && x >= 0 && x < p.S) {
     if (p.in_kind == AY_IN_F32_NCHW) {
@@ -131,13 +131,13 @@ __global__ void prep_input_kernel(FirstConvParams p) {
 }
 
 // ---------------------------------------------------------------- stride-2 gather
-// planes[pl][n][a][b][:] = in[n][2(a-1)+ph][2(b-1)+pw][:]  (padded input coords; zero when
-// out of range), a in [0,Ho+2), b in [0,Wo+2), pl = ph*2+pw.  Output tap (kh,kw) of padded
-// output row m is then row  pl*plane_rows + m + (kh>>1)*(Wo+2) + (kw>>1).
+// Plane pl = ph*2+pw on the consumer's padded OUTPUT grid (Hq x Wq): position (a, b) holds the input pixel with
+// v = (unpadded coordinate) + 1 = (2(a - kPadLo) + ph, 2(b - kPadLo) + pw), zero when that is outside the image.
+// Output tap (kh,kw) of padded output row m is then row  pl*plane_rows + m + (kh>>1)*Wq + (kw>>1).
 __global__ void s2_gather_kernel(const uint4* __restrict__ in, int in_pitch8, int C8, int batch, int H, int W,
                                  uint4* __restrict__ planes, long long plane_rows) {
   const int Ho = H / 2, Wo = W / 2;
-  const int Hq = Ho + 2, Wq = Wo + 2, Hp = H + 2, Wp = W + 2;
+  const int Hq = padded(Ho), Wq = padded(Wo), Hp = padded(H), Wp = padded(W);
   const long long per_plane = (long long)batch * Hq * Wq * C8;
   const long long total = 4 * per_plane;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -150,10 +150,10 @@ __global__ void s2_gather_kernel(const uint4* __restrict__ in, int in_pitch8, in
     r /= Wq;
     const int a = (int)(r % Hq);
     const int n = (int)(r / Hq);
-    const int iy = 2 * (a - 1) + (pl >> 1), ix = 2 * (b - 1) + (pl & 1);
+    const int iy = 2 * (a - kPadLo) + (pl >> 1) - 1, ix = 2 * (b - kPadLo) + (pl & 1) - 1;     // unpadded input pixel
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (iy >= 0 && iy < Hp && ix >= 0 && ix < Wp)
-      v = __ldg(in + ((size_t)((size_t)n * Hp + iy) * Wp + ix) * in_pitch8 + c);
+    if (iy >= 0 && iy < H && ix >= 0 && ix < W)
+      v = __ldg(in + ((size_t)((size_t)n * Hp + iy + kPadLo) * Wp + ix + kPadLo) * in_pitch8 + c);
     planes[((size_t)pl * plane_rows + ((size_t)n * Hq + a) * Wq + b) * C8 + c] = v;
   }
 }
@@ -162,21 +162,20 @@ __global__ void s2_gather_kernel(const uint4* __restrict__ in, int in_pitch8, in
 __global__ void upsample2_kernel(const uint4* __restrict__ in, int in_pitch8, int C8, int batch, int H, int W,
                                  uint4* __restrict__ out, int out_pitch8) {
   const int Ho = 2 * H, Wo = 2 * W;
-  const long long total = (long long)batch * (Ho + 2) * (Wo + 2) * C8;
+  const int Hq = padded(Ho), Wq = padded(Wo);
+  const long long total = (long long)batch * Hq * Wq * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % C8);
     long long r = i / C8;
-    const int x = (int)(r % (Wo + 2));
-    r /= (Wo + 2);
-    const int y = (int)(r % (Ho + 2));
-    const int n = (int)(r / (Ho + 2));
+    const int x = (int)(r % Wq) - kPadLo;
+    r /= Wq;
+    const int y = (int)(r % Hq) - kPadLo;
+    const int n = (int)(r / Hq);
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (y >= 1 && y <= Ho && x >= 1 && x <= Wo) {
-      const int sy = ((y - 1) >> 1) + 1, sx = ((x - 1) >> 1) + 1;
-      v = __ldg(in + ((size_t)((size_t)n * (H + 2) + sy) * (W + 2) + sx) * in_pitch8 + c);
-    }
-    out[((size_t)((size_t)n * (Ho + 2) + y) * (Wo + 2) + x) * out_pitch8 + c] = v;
+    if (y >= 0 && y < Ho && x >= 0 && x < Wo)
+      v = __ldg(in + ((size_t)((size_t)n * padded(H) + (y >> 1) + kPadLo) * padded(W) + (x >> 1) + kPadLo) * in_pitch8 + c);
+    out[((size_t)((size_t)n * Hq + y + kPadLo) * Wq + x + kPadLo) * out_pitch8 + c] = v;
   }
 }
 
@@ -184,28 +183,29 @@ __global__ void upsample2_kernel(const uint4* __restrict__ in, int in_pitch8, in
 __global__ void maxpool_kernel(const void* __restrict__ in, int in_pitch, int Cp, int batch, int H, int W, int stride,
                                void* __restrict__ out, int out_pitch, int is_fp16) {
   const int Ho = (stride == 2) ? H / 2 : H, Wo = (stride == 2) ? W / 2 : W;
-  const long long total = (long long)batch * (Ho + 2) * (Wo + 2) * Cp;
+  const int Hq = padded(Ho), Wq = padded(Wo), Wp = padded(W);
+  const long long total = (long long)batch * Hq * Wq * Cp;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % Cp);
     long long r = i / Cp;
-    const int x = (int)(r % (Wo + 2));
-    r /= (Wo + 2);
-    const int y = (int)(r % (Ho + 2));
-    const int n = (int)(r / (Ho + 2));
+    const int x = (int)(r % Wq) - kPadLo;
+    r /= Wq;
+    const int y = (int)(r % Hq) - kPadLo;
+    const int n = (int)(r / Hq);
     float v = 0.f;
-    if (y >= 1 && y <= Ho && x >= 1 && x <= Wo) {
-      // padded input coordinates of the window's top-left element; the zero halo supplies the
+    if (y >= 0 && y < Ho && x >= 0 && x < Wo) {
+      // top-left element of the window; the zero pixel after each row / image supplies the
       // ZeroPad2d((0,1,0,1)) of the stride-1 variant (models.py:50-51)
-      const int iy = (stride == 2) ? 2 * (y - 1) + 1 : y, ix = (stride == 2) ? 2 * (x - 1) + 1 : x;
-      const size_t base = ((size_t)n * (H + 2) + iy) * (W + 2) + ix;
+      const int iy = y * stride, ix = x * stride;
+      const size_t base = ((size_t)n * padded(H) + iy + kPadLo) * Wp + ix + kPadLo;
       const float a = ld16(in, base * in_pitch + c, is_fp16);
       const float b = ld16(in, (base + 1) * in_pitch + c, is_fp16);
-      const float d = ld16(in, (base + (W + 2)) * in_pitch + c, is_fp16);
-      const float e = ld16(in, (base + (W + 2) + 1) * in_pitch + c, is_fp16);
+      const float d = ld16(in, (base + Wp) * in_pitch + c, is_fp16);
+      const float e = ld16(in, (base + Wp + 1) * in_pitch + c, is_fp16);
       v = fmaxf(fmaxf(a, b), fmaxf(d, e));
     }
-    static_cast<uint16_t*>(out)[(((size_t)n * (Ho + 2) + y) * (Wo + 2) + x) * out_pitch + c] = cvt16(v, is_fp16);
+    static_cast<uint16_t*>(out)[(((size_t)n * Hq + y + kPadLo) * Wq + x + kPadLo) * out_pitch + c] = cvt16(v, is_fp16);
   }
 }
 
@@ -245,7 +245,7 @@ __global__ void dump_nchw_kernel(const void* __restrict__ in, int in_pitch, int 
     r /= H;
     const int c = (int)(r % C);
     const int n = (int)(r / C);
-    out[i] = ld16(in, (((size_t)n * (H + 2) + y + 1) * (W + 2) + x + 1) * in_pitch + c, is_fp16);
+    out[i] = ld16(in, (((size_t)n * padded(H) + y + kPadLo) * padded(W) + x + kPadLo) * in_pitch + c, is_fp16);
   }
 }
 
@@ -254,7 +254,7 @@ __global__ void dump_nchw_kernel(const void* __restrict__ in, int in_pitch, int 
 __global__ void dump_planes_nchw_kernel(const void* __restrict__ planes, long long plane_rows, int pitch, int C, int batch,
                                         int H, int W, int is_fp16, int packed, float* __restrict__ out) {
   const long long total = (long long)batch * C * H * W;
-  const int Hq = H / 2 + 2, Wq = W / 2 + 2;
+  const int Hq = padded(H / 2), Wq = padded(W / 2);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int x = (int)(i % W);
@@ -263,8 +263,8 @@ __global__ void dump_planes_nchw_kernel(const void* __restrict__ planes, long lo
     r /= H;
     const int c = (int)(r % C);
     const int n = (int)(r / C);
-    const int yp = y + 1, xp = x + 1;
-    const size_t pos = ((size_t)n * Hq + (yp >> 1) + 1) * Wq + (xp >> 1) + 1;
+    const int yp = y + 1, xp = x + 1;                       // v = unpadded coordinate + 1 (see s2_gather_kernel)
+    const size_t pos = ((size_t)n * Hq + (yp >> 1) + kPadLo) * Wq + (xp >> 1) + kPadLo;
     if (packed) {
       out[i] = ld16(planes, ((size_t)(yp & 1) * plane_rows + pos) * (2 * pitch) + (xp & 1) * pitch + c, is_fp16);
     } else {
@@ -276,25 +276,24 @@ __global__ void dump_planes_nchw_kernel(const void* __restrict__ planes, long lo
 
 // ---------------------------------------------------------------- reference conv (CUDA cores)
 __global__ void ref_conv_kernel(RefConvParams p) {
-  const int Hq = p.Ho + 2, Wq = p.Wo + 2, Hp = p.H + 2, Wp = p.W + 2;
+  const int Hq = padded(p.Ho), Wq = padded(p.Wo), Hp = padded(p.H), Wp = padded(p.W);
   const long long total = (long long)p.batch * Hq * Wq * p.cout_p;
   const int pad = (p.size - 1) / 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int oc = (int)(i % p.cout_p);
     long long m = i / p.cout_p;
-    const int x = (int)(m % Wq);
-    const int y = (int)((m / Wq) % Hq);
+    const int x = (int)(m % Wq) - kPadLo;                 // unpadded output pixel
+    const int y = (int)((m / Wq) % Hq) - kPadLo;
     const int n = (int)(m / ((long long)Wq * Hq));
-    const bool halo = (y == 0) | (y == Hq - 1) | (x == 0) | (x == Wq - 1);
+    const bool halo = (y < 0) | (y >= p.Ho) | (x < 0) | (x >= p.Wo);
     float acc = 0.f;
     if (!halo) {
       for (int kh = 0; kh < p.size; ++kh)
         for (int kw = 0; kw < p.size; ++kw) {
-          // unpadded input coordinate, then +1 for the halo
-          const int iy = (y - 1) * p.stride + kh - pad + 1, ix = (x - 1) * p.stride + kw - pad + 1;
-          if (iy < 0 || iy >= Hp || ix < 0 || ix >= Wp) continue;
-          const size_t irow = ((size_t)n * Hp + iy) * Wp + ix;
+          const int iy = y * p.stride + kh - pad, ix = x * p.stride + kw - pad;      // unpadded input pixel
+          if (iy < 0 || iy >= p.H || ix < 0 || ix >= p.W) continue;
+          const size_t irow = ((size_t)n * Hp + iy + kPadLo) * Wp + ix + kPadLo;
           const size_t wrow = (size_t)oc * p.ktot + (size_t)(kh * p.size + kw) * p.Cin_k;
           for (int c = 0; c < p.Cin_p; ++c)
             acc = fmaf(ld16(p.in, irow * p.in_pitch + c, p.is_fp16), ld16(p.w, wrow + c, p.is_fp16), acc);
@@ -311,7 +310,7 @@ __global__ void ref_conv_kernel(RefConvParams p) {
 __device__ __forceinline__ float sigmoidf_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 __global__ void decode_kernel(DecodeParams p) {
-  const int Gq = p.G + 2;
+  const int Gq = p.G + p.lo + p.hi;
   const int cout = p.n_anchors * p.dec_cols;
   const long long total = (long long)p.batch * p.G * p.G * cout;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -321,7 +320,7 @@ __global__ void decode_kernel(DecodeParams p) {
     const int gx = (int)(r % p.G);
     const int gy = (int)((r / p.G) % p.G);
     const int n = (int)(r / ((long long)p.G * p.G));
-    const size_t m = ((size_t)n * Gq + gy + 1) * Gq + gx + 1;
+    const size_t m = ((size_t)n * Gq + gy + p.lo) * Gq + gx + p.lo;
     const float t = p.raw[m * p.raw_pitch + ch];
     const int a = ch / p.dec_cols, f = ch - a * p.dec_cols;
     float v;
@@ -344,7 +343,7 @@ inline int grid_for(long long total, int block = 256) {
 }  // namespace
 
 int launch_first_conv(const FirstConvParams& p, cudaStream_t s) {
-  const long long total = (long long)p.batch * (p.S + 2) * (p.S + 2);
+  const long long total = (long long)p.batch * padded(p.S) * padded(p.S);
   const int block = 128;
   const long long grid = (total + block - 1) / block;
   const size_t smem = (size_t)(p.cout * 28) * sizeof(float);
@@ -354,7 +353,7 @@ int launch_first_conv(const FirstConvParams& p, cudaStream_t s) {
 }
 
 int launch_prep_input(const FirstConvParams& p, cudaStream_t s) {
-  const long long total = (long long)p.batch * (p.S + 2) * (p.S + 2);
+  const long long total = (long long)p.batch * padded(p.S) * padded(p.S);
   prep_input_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(p);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
@@ -362,7 +361,7 @@ int launch_prep_input(const FirstConvParams& p, cudaStream_t s) {
 
 int launch_s2_gather(const void* in, int in_pitch, int C8, int batch, int H, int W, void* planes,
                      long long plane_rows, cudaStream_t s) {
-  const long long total = 4LL * batch * (H / 2 + 2) * (W / 2 + 2) * C8;
+  const long long total = 4LL * batch * padded(H / 2) * padded(W / 2) * C8;
   s2_gather_kernel<<<grid_for(total), 256, 0, s>>>(static_cast<const uint4*>(in), in_pitch / 8, C8, batch, H, W,
                                                    static_cast<uint4*>(planes), plane_rows);
   AY_CUDA(cudaGetLastError());
@@ -371,7 +370,7 @@ int launch_s2_gather(const void* in, int in_pitch, int C8, int batch, int H, int
 
 int launch_upsample2(const void* in, int in_pitch, int Cp, int batch, int H, int W, void* out, int out_pitch,
                      cudaStream_t s) {
-  const long long total = (long long)batch * (2 * H + 2) * (2 * W + 2) * (Cp / 8);
+  const long long total = (long long)batch * padded(2 * H) * padded(2 * W) * (Cp / 8);
   upsample2_kernel<<<grid_for(total), 256, 0, s>>>(static_cast<const uint4*>(in), in_pitch / 8, Cp / 8, batch, H, W,
                                                    static_cast<uint4*>(out), out_pitch / 8);
   AY_CUDA(cudaGetLastError());
@@ -385,7 +384,7 @@ int launch_maxpool(const void* in, int in_pitch, int Cp, int batch, int H, int W
     return AY_EINVAL;
   }
   const int Ho = stride == 2 ? H / 2 : H, Wo = stride == 2 ? W / 2 : W;
-  const long long total = (long long)batch * (Ho + 2) * (Wo + 2) * Cp;
+  const long long total = (long long)batch * padded(Ho) * padded(Wo) * Cp;
   maxpool_kernel<<<grid_for(total), 256, 0, s>>>(in, in_pitch, Cp, batch, H, W, stride, out, out_pitch, is_fp16);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
@@ -422,7 +421,7 @@ int launch_dump_planes_nchw(const void* planes, long long plane_rows, int pitch,
 }
 
 int launch_ref_conv(const RefConvParams& p, cudaStream_t s) {
-  const long long total = (long long)p.batch * (p.Ho + 2) * (p.Wo + 2) * p.cout_p;
+  const long long total = (long long)p.batch * padded(p.Ho) * padded(p.Wo) * p.cout_p;
   ref_conv_kernel<<<grid_for(total), 256, 0, s>>>(p);
   AY_CUDA(cudaGetLastError());
   return AY_OK;

@@ -25,12 +25,27 @@ void set_error(const char* fmt, ...);
 
 // ---------------------------------------------------------------------------
 // Activations: zero-haloed NHWC, 16-bit.  A tensor of logical shape [B,C,H,W]
-// is stored as rows of `pitch` elements, one row per PADDED pixel
-//   row(n, y, x) = (n*(H+2) + y)*(W+2) + x,   y in [0,H+2), x in [0,W+2)
-// with the one-pixel halo (y==0, y==H+1, x==0, x==W+1) and channels >= C held at
-// zero.  A 3x3/stride-1 tap (kh,kw) of output row m is then input row
-// m + (kh-1)*(W+2) + (kw-1): every convolution becomes a GEMM over shifted rows.
+// is stored as rows of `pitch` elements, one row per pixel of a PADDED grid of
+// Hp x Wp = (H + kPadLo + 1) x (W + kPadLo + 1) pixels per image:
+//   row(n, y, x) = (n*Hp + y + kPadLo)*Wp + x + kPadLo,   y in [0,H), x in [0,W)
+// with every other pixel of the grid, and channels >= C, held at zero.  A 3x3/stride-1
+// tap (kh,kw) of output row m is then input row m + (kh-1)*Wp + (kw-1): every
+// convolution becomes a GEMM over shifted rows.
+//
+// kPadLo = 0 (default), the SHARED halo: one zero column after each image row and
+// one zero row after each image.  The left neighbour of a row's first pixel is the
+// zero column that ends the previous row, the row above an image's first row is the
+// zero row that ends the previous image (before image 0 the TMA's out-of-bounds fill
+// supplies the zeros), so the frame is paid once instead of twice: the GEMM's M
+// dimension shrinks from (H+2)(W+2) to (H+1)(W+1) rows per image - 13 % fewer MMA
+// rows at 13x13, 7 % at 26x26.  kPadLo = 1 (-DAY_PAD_LO=1) is the classic one-pixel
+// frame of round 1, kept for A/B measurements.
 // ---------------------------------------------------------------------------
+#ifndef AY_PAD_LO
+#define AY_PAD_LO 0
+#endif
+constexpr int kPadLo = AY_PAD_LO;
+__host__ __device__ constexpr int padded(int n) { return n + kPadLo + 1; }
 struct ActView {
   void* ptr = nullptr;   // element (0,0,0, channel 0) of this view
   int C = 0;             // logical channels of the view
@@ -147,6 +162,7 @@ struct DecodeParams {
   const float* raw; int raw_pitch; int batch; int G; int n_anchors; int dec_cols;
   float stride; float anchor_w[8], anchor_h[8];
   float* dec_out; int dec_rows_total, dec_row_off;
+  int lo, hi;            // zero pixels before / after each row and column of `raw`'s padded grid
 };
 int launch_decode(const DecodeParams& p, cudaStream_t s);
 

@@ -123,6 +123,10 @@ __device__ __forceinline__ void tma_load_pair(const CUtensorMap* map, uint32_t c
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(cluster_bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// pixel (py, px) of a padded Hp x Wp grid is one of the zero pixels (kPadLo before, one after each row and column)
+__device__ __forceinline__ bool is_halo(int py, int px, int Hp, int Wp) {
+  return (py < kPadLo) | (py >= Hp - 1) | (px < kPadLo) | (px >= Wp - 1);
+}
 __device__ __forceinline__ unsigned long long global_timer() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -544,7 +548,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const bool in_range = m < p.P;
       int img, yy, xx;
       split_row(m, img, yy, xx);
-      const bool halo = (yy == 0) | (yy == p.Hp - 1) | (xx == 0) | (xx == p.Wp - 1);
+      const bool halo = is_halo(yy, xx, p.Hp, p.Wp);
 
       if (p.dbg & 64) {                                          // ablation: no epilogue work at all
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
@@ -573,26 +577,30 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           t.plane = nullptr;
           t.up = false;
           if (p.up_mode) {
-            // nearest x2 upsample fused (models.py:86-96): interior pixel (py, px) fills the 2x2 block whose top-left
-            // padded coordinate is (2py-1, 2px-1) of the consumer's [2H+2, 2W+2] grid; halo rows write nothing
-            // (their index below wraps and is never dereferenced)
-            const uint32_t Wt = 2u * (uint32_t)(p.Wp - 2) + 2u, Ht = 2u * (uint32_t)(p.Hp - 2) + 2u;
+            // nearest x2 upsample fused (models.py:86-96): pixel (y, x) fills the 2x2 block whose top-left pixel is
+            // (2y, 2x) of the consumer's grid, i.e. padded (2py - kPadLo, 2px - kPadLo); halo rows write nothing
+            // (their index below may wrap and is never dereferenced)
+            const uint32_t Wt = (uint32_t)padded(2 * (p.Wp - kPadLo - 1)), Ht = (uint32_t)padded(2 * (p.Hp - kPadLo - 1));
             t.up = t.store;
-            const uint32_t row = ((uint32_t)image * Ht + (uint32_t)(2 * py - 1)) * Wt + (uint32_t)(2 * px - 1);
+            const uint32_t row = ((uint32_t)image * Ht + (uint32_t)(2 * py - kPadLo)) * Wt + (uint32_t)(2 * px - kPadLo);
             t.out = at(p.out_ptr, row, (uint32_t)p.out_pitch * 2u, n0b);
           } else {
             t.out = at(p.out_ptr, (uint32_t)mr, (uint32_t)p.out_pitch * 2u, n0b);
           }
           if (p.plane_mode != 0) {
-            // padded output pixel (py, px) -> plane (py&1, px&1), position (py/2 + 1, px/2 + 1) of the half-size padded grid
-            const uint32_t Hq2 = (uint32_t)(p.Hp - 2) / 2u + 2u, Wq2 = (uint32_t)(p.Wp - 2) / 2u + 2u;
-            const uint32_t pos = ((uint32_t)image * Hq2 + (uint32_t)(py >> 1) + 1u) * Wq2 + (uint32_t)(px >> 1) + 1u;
+            // Parity planes of the stride-2 consumer, laid out on ITS padded output grid so that its taps are row shifts:
+            // with v = (unpadded coordinate) + 1 (v = 0 is the zero pixel before the row / column), pixel (vy, vx) goes
+            // to plane (vy&1, vx&1) at position (vy/2 + kPadLo, vx/2 + kPadLo); the consumer's tap (kh, kw) of output
+            // row m is then row m + (kh>>1)*Wq + (kw>>1) of plane (kh&1, kw&1).
+            const int vy = py + 1 - kPadLo, vx = px + 1 - kPadLo;
+            const uint32_t Hq2 = (uint32_t)padded((p.Hp - kPadLo - 1) / 2), Wq2 = (uint32_t)padded((p.Wp - kPadLo - 1) / 2);
+            const uint32_t pos = ((uint32_t)image * Hq2 + (uint32_t)((vy >> 1) + kPadLo)) * Wq2 + (uint32_t)((vx >> 1) + kPadLo);
             const uint32_t prow_n = (uint32_t)p.plane_rows, pitch_b = (uint32_t)p.plane_pitch * 2u;
             if (p.plane_packed) {
-              // row-parity plane, 2 x pitch channels per row: [pixel with even padded x | pixel with odd padded x]
-              t.plane = at(p.planes, (uint32_t)(py & 1) * prow_n + pos, 2u * pitch_b, (uint32_t)(px & 1) * pitch_b + n0b);
+              // row-parity plane, 2 x pitch channels per row: [pixel with even vx | pixel with odd vx]
+              t.plane = at(p.planes, (uint32_t)(vy & 1) * prow_n + pos, 2u * pitch_b, (uint32_t)(vx & 1) * pitch_b + n0b);
             } else {
-              t.plane = at(p.planes, (uint32_t)((py & 1) * 2 + (px & 1)) * prow_n + pos, pitch_b, n0b);
+              t.plane = at(p.planes, (uint32_t)((vy & 1) * 2 + (vx & 1)) * prow_n + pos, pitch_b, n0b);
             }
           }
           return t;
@@ -638,7 +646,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const int mr = m + c * kRowsPerCta;
               int px, py, image;
               split_row(mr, image, py, px);
-              t = row_target(mr, image, py, px, (py == 0) | (py == p.Hp - 1) | (px == 0) | (px == p.Wp - 1));
+              t = row_target(mr, image, py, px, is_halo(py, px, p.Hp, p.Wp));
               ch = 0;
             }
             // fp32 pairs (add/mul.f32x2: FADD2 / FMUL2, same IEEE results as the scalar forms, half the instructions)
@@ -668,7 +676,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (i + 2 < kMaxChunksPerWarp) load_residual(i + 2);
             if (p.up_mode) {
               if (t.up && !(p.dbg & 4)) {
-                const size_t down = (size_t)(2 * (p.Wp - 2) + 2) * p.out_pitch;      // one row of the upsampled grid
+                const size_t down = (size_t)padded(2 * (p.Wp - kPadLo - 1)) * p.out_pitch;      // one row of the upsampled grid
 #pragma unroll
                 for (int d = 0; d < 4; ++d) {
                   uint16_t* dst = t.out + (d >> 1) * down + (d & 1) * p.out_pitch + ch;
@@ -693,8 +701,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
         fence_after();
         const uint32_t t_acc = tmem_base + (uint32_t)(acc * acc_cols) + lane_addr;
-        const int Gd = p.Wp - 2;
-        const int gx = xx - 1, gy = yy - 1;
+        const int Gd = p.Wp - kPadLo - 1;
+        const int gx = xx - kPadLo, gy = yy - kPadLo;
         float* obase = p.dec_out + ((size_t)img * p.dec_rows_total + p.dec_row_off) * p.dec_cols +
                        ((size_t)gy * Gd + gx) * p.dec_cols;
         const size_t a_step = (size_t)Gd * Gd * p.dec_cols;

@@ -203,7 +203,9 @@ void free_network(ay_ctx* ctx) {
   ctx->idx_src_h = ctx->idx_src_w = -1;
 }
 
-long long padded_rows(int batch, int H, int W) { return (long long)batch * (H + 2) * (W + 2); }
+long long padded_rows(int batch, int H, int W) { return (long long)batch * padded(H) * padded(W); }
+// the fp32 accuracy mode keeps the classic one-pixel frame (fp32_path.cu)
+long long padded_rows_f32(int batch, int H, int W) { return (long long)batch * (H + 2) * (W + 2); }
 
 int alloc_view(ay_ctx* ctx, ActView* v, int C, int H, int W) {
   v->C = C;
@@ -421,10 +423,10 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
   if (ctx->is_f32) {
     if (in_channels != 3) { set_error("fp32 mode: the input must have 3 channels"); return AY_EINVAL; }
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->f_in),
-                         sizeof(float) * (size_t)ay::padded_rows(max_batch, img_size, img_size) * 3, true));
+                         sizeof(float) * (size_t)ay::padded_rows_f32(max_batch, img_size, img_size) * 3, true));
     for (int i = 0; i < n_layers; ++i) {
       Layer& L = Ls[i];
-      const size_t elems = (size_t)ay::padded_rows(max_batch, L.H, L.W) * L.C;
+      const size_t elems = (size_t)ay::padded_rows_f32(max_batch, L.H, L.W) * L.C;
       switch (L.d.type) {
         case AY_CONV:
           L.impl = 4;
@@ -811,14 +813,14 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
           int off = 0;
           for (int k = 0; k < L.d.n_src; ++k) {
             const Layer& S = Ls[L.d.src[k]];
-            AY_TRY(ay::launch_f32_copy_channels(S.f_out, S.C, ay::padded_rows(batch, S.H, S.W), L.f_out + off, L.C, st));
+            AY_TRY(ay::launch_f32_copy_channels(S.f_out, S.C, ay::padded_rows_f32(batch, S.H, S.W), L.f_out + off, L.C, st));
             ++ctx->launches;
             off += S.C;
           }
         }
         break;
       case AY_SHORTCUT:
-        AY_TRY(ay::launch_f32_add(prev, Ls[L.d.src[0]].f_out, ay::padded_rows(batch, L.H, L.W) * L.C, L.f_out, st));
+        AY_TRY(ay::launch_f32_add(prev, Ls[L.d.src[0]].f_out, ay::padded_rows_f32(batch, L.H, L.W) * L.C, L.f_out, st));
         ++ctx->launches;
         break;
       case AY_YOLO: {
@@ -832,6 +834,7 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
           d.anchor_h[a] = (float)((double)L.d.anchors[2 * a + 1] / stride);
         }
         d.dec_out = dec_out; d.dec_rows_total = ctx->dec_rows; d.dec_row_off = L.dec_row_off;
+        d.lo = 1; d.hi = 1;
         AY_TRY(ay::launch_decode(d, st));
         ++ctx->launches;
         break;
@@ -861,7 +864,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   }
   static const ActView no_view;
   const ActView& in = L.first ? no_view : Ls[i - 1].out;
-  const int Hq = L.H + 2, Wq = L.W + 2;
+  const int Hq = ay::padded(L.H), Wq = ay::padded(L.W);
   const ActView* res = L.residual_src >= 0 ? &Ls[L.residual_src].out : nullptr;
   const Layer* Y = L.is_head ? &Ls[L.yolo_layer] : nullptr;
 
@@ -885,6 +888,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
         d.anchor_h[a] = (float)((double)Y->d.anchors[2 * a + 1] / ((double)ctx->img_size / (double)L.H));
       }
       d.dec_out = dec_out; d.dec_rows_total = ctx->dec_rows; d.dec_row_off = Y->dec_row_off;
+      d.lo = ay::kPadLo; d.hi = 1;
       ++ctx->launches;
       AY_TRY(ay::launch_decode(d, st));
     }
