@@ -65,8 +65,15 @@ struct ConvGemmParams {
   int n_groups;          // A boxes per k-block
   int kb_per_tap;        // ceil(Cin / 64)
   int k16_all, k16_last; // K=16 MMA steps of a 64-channel k-block that hold data: all taps of a group / its last tap (0 = 4)
-  int a_row_off[9];      // row offset of group g's A box
-  int b_tap0[9];         // first weight tap of group g (K layout is tap-major)
+  int a_row_off[27];     // row offset of group g's A box
+  int b_tap0[27];        // first weight tap of group g (K layout is tap-major)
+  // fp32 accuracy mode on the tensor cores (kind::tf32, 3-pass split): a group is (pass, tap group); pass 0 contracts
+  // A_lo x W_hi, pass 1 A_hi x W_lo, pass 2 A_hi x W_hi (small terms first, see engine.cu).  The activation rows hold [hi | lo] side by side and the weight
+  // rows [W_hi | W_lo], so a pass is a column offset into each (elements)
+  int a_col_off[27], b_col_off[27];
+  int tf32_na;           // tf32 mode: accumulators per tile, summed in the epilogue (1, 2 or 4)
+  int tf32;              // 1: fp32 operands (32 channels per 128-byte k-block), plain fp32 row store epilogue
+  int pad_lo;            // tf32 mode: zero pixels before each row / column of the OUTPUT grid (the fp32 path keeps a full frame)
   int a_rows;            // rows of the A box (128, or 130 with tap reuse)
   int BN;                // N of the pair tile (each CTA loads BN/2 weight rows)
   int num_stages;
@@ -116,7 +123,7 @@ constexpr int kProfStampBase = 16;
 constexpr int kProfStampCtas = 160;                       // >= CTAs per launch (148)
 constexpr int kProfWords = kProfStampBase + 4 * kProfStampCtas;
 int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p, int G, int is_fp16,
-                     int num_sms, cudaStream_t stream);
+                     int num_sms, cudaStream_t stream);   // is_fp16: 0 bf16, 1 fp16, 2 tf32 (p.tf32 set)
 int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident);
 void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int extra_bytes, int* stages, int* nbuf);
 #ifndef AY_EPI_PARTS
@@ -179,6 +186,12 @@ struct F32ConvParams {
   float* out; int out_pitch; int Ho, Wo; int batch;
 };
 int launch_f32_prep(const F32PrepParams& p, cudaStream_t s);
+// v -> [hi | lo] with hi = v rounded to tf32 (10-bit mantissa, round to nearest) and lo = v - hi (exact): rows of C floats
+// in, rows of 2C floats out
+int launch_f32_split(const float* in, int in_pitch, int C, long long rows, float* out, cudaStream_t s);
+// parity planes (classic one-pixel frame) of a [B,H,W] fp32 tensor with `pitch` floats per pixel, for stride-2 convolutions
+int launch_f32_s2_gather(const float* in, int pitch, int batch, int H, int W, float* planes, long long plane_rows,
+                         cudaStream_t s);
 int launch_f32_conv(const F32ConvParams& p, cudaStream_t s);
 int launch_f32_maxpool(const float* in, int C, int batch, int H, int W, int size, int stride, float* out, cudaStream_t s);
 int launch_f32_upsample2(const float* in, int C, int batch, int H, int W, float* out, cudaStream_t s);

@@ -146,6 +146,15 @@ __device__ __forceinline__ void umma2_f16(uint32_t d_tmem, uint64_t a_desc, uint
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
       : "memory");
 }
+// fp32 accuracy mode: the same instruction on tf32 operands (32-bit elements, the low 13 mantissa bits ignored), K = 8
+__device__ __forceinline__ void umma2_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+      : "memory");
+}
 // arrive on the mbarrier at the same shared-memory offset in both CTAs once all prior MMAs retire
 __device__ __forceinline__ void umma2_commit(uint32_t bar) {
   asm volatile(
@@ -246,7 +255,11 @@ __device__ __forceinline__ void append_candidates(const ConvGemmParams& p, bool 
 }
 
 // G = taps per pipeline stage (3: the kw taps of one kh share one 130-row A box; 1: one tap per stage)
-template <int G, bool FP16, bool SPLIT>
+// TF32: fp32 accuracy mode (precision = "fp32" on the tensor cores).  Operands are fp32 rows ([hi | lo] activations,
+// [W_hi | W_lo] weights), a 128-byte k-block is 32 channels, and a "group" is (pass, tap group) with the three passes
+// A_hi W_hi + A_lo W_hi + A_hi W_lo accumulated in the same fp32 TMEM tile: the product carries ~22 mantissa bits.  The
+// epilogue is a plain bias + LeakyReLU + fp32 row store (the fp32 network keeps one kernel per cfg block, fp32_path.cu).
+template <int G, bool FP16, bool SPLIT, bool TF32>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ ConvGemmParams p) {
@@ -264,7 +277,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // loaded, multiplied and handed over together - one barrier round per R blocks instead of one per block
   const int R = p.m_batch;
   const int tile_rows = 2 * kRowsPerCta * R;
-  const int acc_cols = p.BN * R;
+  // tf32 mode: a tile accumulates round-robin into NA accumulators (unit u -> accumulator u % NA) that the epilogue adds
+  // with round-to-nearest: the tensor core's truncating accumulation then acts on NA shorter, smaller partial sums
+  const int NA = TF32 ? p.tf32_na : 1;
+  const int acc_cols = p.BN * R * NA;
   // tiles of <= 4 chunks (32 accumulator columns each): the two epilogue warps of a TMEM lane quarter take alternate tiles
   // (SPLIT: chosen by launch_conv_gemm - a single chunk, or up to kMaxChunksPerWarp chunks of a non-head layer)
   constexpr bool tile_split = SPLIT;
@@ -286,6 +302,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // would be an L2 round trip in the middle of the epilogue's dependency chain
   float* s_bias = reinterpret_cast<float*>(smem_raw + (((tmem_slot + 4u + 15u) & ~15u) - smem_addr(smem_raw)));
 
+  constexpr int kBKe = TF32 ? 32 : kBK;            // channels per 128-byte k-block
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   // attribution stamps (profiling runs only): %globaltimer at entry / after the prologue / at exit of every CTA, and
@@ -388,12 +405,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (load) {
               const int arow = m0 + p.a_row_off[g];
               if (p.a_mode == 1) tma_load_pair(&tmA, lead_full, sa, 0, arow >> 3);   // 8 pixels per 128-byte row
-              else tma_load_pair(&tmA, lead_full, sa, kb * kBK, arow);
+              else tma_load_pair(&tmA, lead_full, sa, kb * kBKe + (TF32 ? p.a_col_off[g] : 0), arow);
               if (!p.b_resident) {
-                const int bcol0 = g * G * p.kb_per_tap * kBK;       // weight taps of group g are g*G .. g*G+G-1
+                // weight taps of group g are g*G .. g*G+G-1 (tf32: first tap and pass column from the tables)
+                const int bcol0 = TF32 ? p.b_tap0[g] * p.kb_per_tap * kBKe + p.b_col_off[g] : g * G * p.kb_per_tap * kBKe;
 #pragma unroll
                 for (int j = 0; j < G; ++j)
-                  tma_load_pair(&tmB, lead_full, sa + a_region + j * b_tile, bcol0 + (j * p.kb_per_tap + kb) * kBK, n0);
+                  tma_load_pair(&tmB, lead_full, sa + a_region + j * b_tile, bcol0 + (j * p.kb_per_tap + kb) * kBKe, n0);
               }
             }
             if (++kb == p.kb_per_tap) { kb = 0; ++g; }
@@ -408,7 +426,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     if (leader) {
       // instruction descriptor: D=f32, A/B = bf16|f16, both K-major, N = BN, M = 256 (pair)
-      constexpr uint32_t fmt = FP16 ? 0u : 1u;
+      constexpr uint32_t fmt = TF32 ? 2u : FP16 ? 0u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(p.BN >> 3) << 17) |
                              ((uint32_t)((2 * kRowsPerCta) >> 4) << 24);
       // descriptor constants: SWIZZLE_128B (2 << 61), version 1 (1 << 46), SBO = 1024 B (64 << 32).  Tap j of a group
@@ -444,6 +462,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // shows up in the layer time
         uint32_t first = 0u;                               // 0 for the very first MMA of the tile (overwrite D)
         int g = 0, kb = 0;
+        int uix = 0;                                       // tf32: running unit index of the tile (accumulator = uix % NA)
         for (int st = 0; st < stages_per_tile; ++st) {
           const long long c1 = prof ? clock64() : 0;
           bar_wait(full_bar(stage), phase, p.err_flag, 3);
@@ -480,13 +499,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                   const int ks = j == G - 1 ? k16_last : k16_all;
 #pragma unroll
                   for (int k = 0; k < kBK / 16; ++k)
-                    if (k < ks)
-                      umma2_f16(d_tmem, a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k), b0 + (uint64_t)(j * b_step + 2 * k), idesc,
-                                first | (uint32_t)(j | k));
+                    if (k < ks) {
+                      if (TF32) umma2_tf32(d_tmem + (uint32_t)((uix % NA) * p.BN), a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k),
+                                           b0 + (uint64_t)(j * b_step + 2 * k), idesc, (uix >= NA ? 1u : 0u) | (uint32_t)(j | k));
+                      else umma2_f16(d_tmem, a0 + (uint64_t)(j * (kRowBytes >> 4) + 2 * k), b0 + (uint64_t)(j * b_step + 2 * k), idesc,
+                                     first | (uint32_t)(j | k));
+                    }
                 }
               }
             }
             first = 1u;
+            ++uix;
             if (++kb == p.kb_per_tap) { kb = 0; ++g; }
           }
           if (el) umma2_commit(empty_bar(stage));   // frees this stage in both CTAs
@@ -513,7 +536,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int row_in_tile = quarter * 32 + lane;
     const uint32_t lane_addr = ((uint32_t)(quarter * 32)) << 16;
     const int hw = p.Hp * p.Wp;
-    const int nchunks = (p.BN >> 5) * R;
+    const int nchunks = (p.BN >> 5) * R;                    // (tf32: per accumulator; the NA accumulators are summed)
     // A tile with a single 32-column chunk would leave half of the epilogue warps idle and make the per-tile
     // latency chain (wait, tcgen05.ld, math, store, arrive) the bound; there the two warps of a quarter take
     // alternate TILES instead of alternate chunks (tile parity = accumulator buffer = `half`).
@@ -553,6 +576,38 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (p.dbg & 64) {                                          // ablation: no epilogue work at all
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
         fence_after();
+      } else if (TF32) {
+        // fp32 accuracy mode: bias + LeakyReLU in fp32 (one rounding each, as fp32_path.cu), 128 bytes per row and chunk
+        const bool store = in_range && !((yy < p.pad_lo) | (yy >= p.Hp - 1) | (xx < p.pad_lo) | (xx >= p.Wp - 1));
+        bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
+        fence_after();
+        const uint32_t t_acc = tmem_base + (uint32_t)(acc * acc_cols) + lane_addr;
+        float* orow = static_cast<float*>(p.out_ptr) + (size_t)m * p.out_pitch + n0;
+#pragma unroll
+        for (int i = 0; i < kMaxChunksPerWarp; ++i) {
+          const int c = c_first + c_step * i;
+          if (c < nchunks) {
+            uint32_t v[32];
+            tmem_load32(t_acc + (uint32_t)(c * 32), v);
+            for (int sub = 1; sub < NA; ++sub) {
+              uint32_t w[32];
+              tmem_load32(t_acc + (uint32_t)(sub * p.BN + c * 32), w);
+#pragma unroll
+              for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__fadd_rn(__uint_as_float(v[e]), __uint_as_float(w[e])));
+            }
+            const float* bias = s_bias + n0 + c * 32;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              float y = __fadd_rn(__uint_as_float(v[e]), bias[e]);
+              if (p.leaky) y = y > 0.f ? y : __fmul_rn(y, 0.1f);
+              v[e] = __float_as_uint(y);
+            }
+            if (store && !(p.dbg & 4)) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) stg256(orow + c * 32 + q * 8, &v[q * 8]);
+            }
+          }
+        }
       } else if (!p.head) {
         // Thread = output row.  All global traffic of the epilogue is 256-bit per thread (one full 32-byte sector, two per
         // 32-channel chunk): the residual is read straight into registers BEFORE waiting for the accumulator, so its
@@ -915,17 +970,30 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvG
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = p.pdl ? 1 : 0;
-#define AY_LAUNCH3(GG, FF, SS)                                                                                             \
-  do {                                                                                                                     \
-    AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<GG, FF, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));  \
-    AY_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<GG, FF, SS>, tmA, tmB, p));                                          \
+#define AY_LAUNCH4(GG, FF, SS, TT)                                                                                            \
+  do {                                                                                                                        \
+    AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<GG, FF, SS, TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
+    AY_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<GG, FF, SS, TT>, tmA, tmB, p));                                         \
   } while (0)
+#define AY_LAUNCH3(GG, FF, SS) AY_LAUNCH4(GG, FF, SS, false)
+  if (p.tf32) {
+    if (p.head || p.has_res || p.b_resident || p.a_mode != 0 || p.m_batch != 1 || (G != 1 && G != 3) || p.tf32_na < 1 ||
+        p.BN * p.tf32_na * p.num_acc > 512) {
+      set_error("conv_gemm: tf32 mode supports plain 1x1 / 3x3 tiles only");
+      return AY_EINVAL;
+    }
+    if (G == 3) { if (split) AY_LAUNCH4(3, false, true, true); else AY_LAUNCH4(3, false, false, true); }
+    else        { if (split) AY_LAUNCH4(1, false, true, true); else AY_LAUNCH4(1, false, false, true); }
+    AY_CUDA(cudaGetLastError());
+    return AY_OK;
+  }
 #define AY_LAUNCH(GG, FF) do { if (split) AY_LAUNCH3(GG, FF, true); else AY_LAUNCH3(GG, FF, false); } while (0)
   if (G == 3) { if (is_fp16) AY_LAUNCH(3, true); else AY_LAUNCH(3, false); }
   else if (G == 2) { if (is_fp16) AY_LAUNCH(2, true); else AY_LAUNCH(2, false); }
   else        { if (is_fp16) AY_LAUNCH(1, true); else AY_LAUNCH(1, false); }
 #undef AY_LAUNCH
 #undef AY_LAUNCH3
+#undef AY_LAUNCH4
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

@@ -58,12 +58,14 @@ int make_map_2d(CUtensorMap* map, void* base, int inner, long long rows, int pit
     return AY_ECUDA;
   }
   cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+  const int esz = is_fp16 == 2 ? 4 : 2;                    // is_fp16: 0 bf16, 1 fp16, 2 fp32 (tf32 operands)
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * esz};
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   const CUtensorMapSwizzle sw = !swizzle ? CU_TENSOR_MAP_SWIZZLE_NONE
-                                : (box_inner * 2 == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-  CUresult r = enc(map, is_fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims,
+                                : (box_inner * esz == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  CUresult r = enc(map, is_fp16 == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                        : is_fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims,
                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -143,6 +145,7 @@ struct Layer {
   // fp32 accuracy mode (AY_F32, fp32_path.cu): zero-haloed NHWC fp32 rows, pitch = C; weights [K][Cout]
   float* f_out = nullptr;
   float* f_w = nullptr;
+  float* f_w2 = nullptr;            // tensor-core variant (impl 5): [Cout][2 * taps * Cin] = [W_hi | W_lo], K order (tap, c)
 };
 
 }  // namespace
@@ -158,7 +161,11 @@ struct ay_ctx {
   bool built = false, finalized = false, use_ref = false;
   bool is_f32 = false;                // AY_F32 network: every block runs the fp32 kernels of fp32_path.cu
   float* f_in = nullptr;              // AY_F32: staged input [B,S+2,S+2,3]
+  float* f_split = nullptr;           // AY_F32, tensor-core convolutions: [hi | lo] copy of the current conv's input rows
+  float* f_planes = nullptr;          // ... and its parity planes when the conv has stride 2
+  size_t f_split_floats = 0, f_planes_floats = 0;
   int dbg = 0;                        // AY_DBG ablation bits (see ConvGemmParams::dbg)
+  int tf32_na = 2;                    // AY_F32 tensor-core convolutions: accumulators per tile (AY_TF32_NA = 1 | 2 | 4)
   bool no_head_fast = false;          // AY_NO_HEADFAST=1: generic decode epilogue for every head
   bool pdl = true;                    // chain the convolution launches with programmatic dependent launch (AY_NO_PDL=1: off)
   int dec_rows = 0, dec_cols = 0;
@@ -201,6 +208,8 @@ void free_network(ay_ctx* ctx) {
   ctx->built = ctx->finalized = false;
   ctx->idx_y = ctx->idx_x = nullptr;
   ctx->idx_src_h = ctx->idx_src_w = -1;
+  ctx->f_split = ctx->f_planes = nullptr;
+  ctx->f_split_floats = ctx->f_planes_floats = 0;
 }
 
 long long padded_rows(int batch, int H, int W) { return (long long)batch * padded(H) * padded(W); }
@@ -276,6 +285,7 @@ extern "C" int ay_create(ay_ctx** out, int device) {
   if (const char* e = getenv("AY_DBG")) ctx->dbg = atoi(e);
   if (getenv("AY_NO_PDL")) ctx->pdl = false;
   if (getenv("AY_NO_HEADFAST")) ctx->no_head_fast = true;
+  if (const char* e = getenv("AY_TF32_NA")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) ctx->tf32_na = v; }
   *out = ctx;
   return AY_OK;
 }
@@ -430,6 +440,31 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       switch (L.d.type) {
         case AY_CONV:
           L.impl = 4;
+          // Tensor-core variant (3 x tf32): every convolution whose channel counts are multiples of 32 - all but the
+          // first layer and the heads of the shipped cfgs, > 99.5 % of the FLOPs.  AY_F32_FFMA=1 keeps the CUDA-core
+          // kernel everywhere (cross-check and A/B).
+          if (L.cin % 32 == 0 && L.C % 32 == 0 && !getenv("AY_F32_FFMA")) {
+            L.impl = 5;
+            const int taps = L.d.size * L.d.size;
+            L.ktot = taps * L.cin;
+            // N tile of at most 128 columns, so that a tile can spread its MMAs over several accumulators (tf32_na)
+            const int bn_cap = getenv("AY_TF32_BN") ? atoi(getenv("AY_TF32_BN")) : 128;
+            L.BN = (L.C % 128 == 0 && bn_cap >= 128) ? 128 : (L.C % 64 == 0 && bn_cap >= 64) ? 64 : 32;
+            L.cout_rows = L.C;
+            L.G = (L.d.size == 3 && L.d.stride == 1) ? 3 : 1;
+            L.a_rows = L.G == 3 ? 130 : 128;
+            L.units_per_stage = 1;
+            ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, 0, 1, 0, &L.stages, &L.nbuf);
+            if (L.stages < 2) { set_error("layer %d: tf32 tile does not fit in shared memory", i); return AY_EINVAL; }
+            AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_w2), sizeof(float) * (size_t)L.C * 2 * L.ktot, true));
+            const int iH = i ? Ls[i - 1].H : img_size, iW = i ? Ls[i - 1].W : img_size;
+            ctx->f_split_floats = std::max(ctx->f_split_floats, (size_t)ay::padded_rows_f32(max_batch, iH, iW) * 2 * L.cin);
+            if (L.d.stride == 2) {
+              if (L.d.size != 3 || (iH & 1) || (iW & 1)) { set_error("layer %d: stride-2 conv needs size 3 and even input", i); return AY_EINVAL; }
+              L.plane_rows = ay::padded_rows_f32(max_batch, L.H, L.W);
+              ctx->f_planes_floats = std::max(ctx->f_planes_floats, (size_t)(4 * L.plane_rows * 2 * L.cin));
+            }
+          }
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_w), sizeof(float) * (size_t)L.d.size * L.d.size * L.cin * L.C, false));
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.C, true));
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_out), sizeof(float) * elems, true));
@@ -445,6 +480,18 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_out), sizeof(float) * elems, true));
           break;
       }
+    }
+    if (ctx->f_split_floats) AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->f_split), sizeof(float) * ctx->f_split_floats, true));
+    if (ctx->f_planes_floats) AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->f_planes), sizeof(float) * ctx->f_planes_floats, true));
+    for (int i = 0; i < n_layers; ++i) {
+      Layer& L = Ls[i];
+      if (L.d.type != AY_CONV || L.impl != 5) continue;
+      const int iH = i ? Ls[i - 1].H : img_size, iW = i ? Ls[i - 1].W : img_size;
+      AY_TRY(ay::make_map_2d(&L.tmB, L.f_w2, 2 * L.ktot, L.C, 2 * L.ktot, 32, L.BN / 2, 2));
+      if (L.d.stride == 2)
+        AY_TRY(ay::make_map_2d(&L.tmA, ctx->f_planes, 2 * L.cin, 4 * L.plane_rows, 2 * L.cin, 32, L.a_rows, 2));
+      else
+        AY_TRY(ay::make_map_2d(&L.tmA, ctx->f_split, 2 * L.cin, ay::padded_rows_f32(max_batch, iH, iW), 2 * L.cin, 32, L.a_rows, 2));
     }
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_y), sizeof(int) * img_size, true));
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_x), sizeof(int) * img_size, true));
@@ -674,6 +721,45 @@ extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const flo
         for (int t = 0; t < taps; ++t) r[((size_t)t * cin + c) * cout + o] = w[((size_t)o * cin + c) * taps + t];
     AY_CUDA(cudaMemcpy(L.f_w, r.data(), r.size() * sizeof(float), cudaMemcpyHostToDevice));
     AY_CUDA(cudaMemcpy(L.bias, bias, sizeof(float) * cout, cudaMemcpyHostToDevice));
+    if (L.impl == 5) {
+      // [W_hi | W_lo] per output channel, K order (tap, c): hi = w rounded to tf32, lo = w - hi (exact in fp32).
+      //
+      // De-biasing of the accumulation.  The tensor core adds each K=8 MMA into the fp32 accumulator with TRUNCATION: the
+      // running sum loses on average half an ulp of itself per MMA, E = 0.5 * 0.7213 * 2^-23 = 4.3e-8 relative (0.7213 =
+      // mean of 1/mantissa).  The term contributed by the q-th of the n = K/8 MMAs of the final (A_hi x W_hi) pass is part
+      // of the sum for the remaining n - q truncations, so it arrives shrunk by (n - q) * E: measured as a coherent
+      // 5e-5 shrink of the deepest head, 5e-4 on small elements that are differences of large partial sums.  The expected
+      // loss is linear in the terms, so it is restored exactly (in expectation, for every element) by inflating each
+      // weight by its own factor (1 + (n - q) * E).  W_hi cannot carry a 1e-5 change (10-bit mantissa), W_lo can: the
+      // inflation is added there, no extra pass.  q follows the kernel's issue order (tap group, k-block, tap, K=8 step).
+      // The factor 0.75 is calibrated on the B200 (sweep of AY_TF32_KAPPA over 0 .. 2 against the float64 oracle: the
+      // deepest raw head of yolov3-custom is off by 5.0e-5 of its range without the ramp, 3.8e-6 at 0.75, 1.1e-5 at 1.0):
+      // the adder keeps a little more than the 24 stored bits before it truncates.
+      const double E = 0.5 * 0.7213 / 8388608.0 * (getenv("AY_TF32_KAPPA") ? atof(getenv("AY_TF32_KAPPA")) : 0.75);
+      const int Gt = L.G, kbpt = cin / 32;
+      // units (tap group, k-block) of a pass; the final pass's units are U = 2*units .. 3*units-1 of the tile and unit U
+      // accumulates into accumulator U % NA: position of each unit among ITS accumulator's final-pass units
+      const int units = (taps / Gt) * kbpt, NAw = ctx->tf32_na;
+      std::vector<int> upos(units), ucnt(NAw, 0);
+      for (int i2 = 0; i2 < units; ++i2) upos[i2] = ucnt[(2 * units + i2) % NAw]++;
+      std::vector<float> r2((size_t)cout * 2 * L.ktot);
+      for (int o = 0; o < cout; ++o)
+        for (int c = 0; c < cin; ++c)
+          for (int t = 0; t < taps; ++t) {
+            const float v = w[((size_t)o * cin + c) * taps + t];
+            uint32_t u;
+            memcpy(&u, &v, 4);
+            u = (u + 0x1000u) & 0xFFFFE000u;
+            float hi;
+            memcpy(&hi, &u, 4);
+            const int unit = (t / Gt) * kbpt + c / 32;
+            const int q = (upos[unit] * Gt + t % Gt) * 4 + (c % 32) / 8;                    // MMAs before this one in its accumulator
+            const int n_mma = ucnt[(2 * units + unit) % NAw] * Gt * 4;
+            r2[(size_t)o * 2 * L.ktot + (size_t)t * cin + c] = hi;
+            r2[(size_t)o * 2 * L.ktot + L.ktot + (size_t)t * cin + c] = (float)((double)v * (1.0 + (double)(n_mma - q) * E) - (double)hi);
+          }
+      AY_CUDA(cudaMemcpy(L.f_w2, r2.data(), r2.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
     L.weights_set = true;
     ctx->finalized = false;
     return AY_OK;
@@ -792,6 +878,62 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
     const int pC = i ? Ls[i - 1].C : 3, pH = i ? Ls[i - 1].H : ctx->img_size, pW = i ? Ls[i - 1].W : ctx->img_size;
     switch (L.d.type) {
       case AY_CONV: {
+        if (L.impl == 5) {
+          // [hi | lo] copy of the input rows, parity planes for stride 2, then the 3-pass tf32 GEMM
+          AY_TRY(ay::launch_f32_split(prev, pC, L.cin, ay::padded_rows_f32(batch, pH, pW), ctx->f_split, st));
+          ++ctx->launches;
+          if (L.d.stride == 2) {
+            AY_TRY(ay::launch_f32_s2_gather(ctx->f_split, 2 * L.cin, batch, pH, pW, ctx->f_planes, L.plane_rows, st));
+            ++ctx->launches;
+          }
+          const int Wq = L.W + 2, taps = L.d.size * L.d.size;
+          ay::ConvGemmParams g{};
+          g.tf32 = 1; g.pad_lo = 1;
+          g.P = (int)ay::padded_rows_f32(batch, L.H, L.W);
+          g.m_batch = 1;
+          g.num_m_tiles = (g.P + 255) / 256;
+          g.num_n_tiles = L.C / L.BN;
+          g.a_rows = L.a_rows;
+          g.kb_per_tap = L.cin / 32;
+          g.k16_all = g.k16_last = 4;
+          const int tg = L.d.size == 1 ? 1 : L.d.stride == 1 ? 3 : 9;        // tap groups (A boxes) per pass
+          g.n_groups = 3 * tg;
+          for (int pass = 0; pass < 3; ++pass)
+            for (int t = 0; t < tg; ++t) {
+              const int gi = pass * tg + t;
+              long long off = 0;
+              int tap0 = 0;
+              if (L.d.size == 3 && L.d.stride == 1) { off = (long long)(t - 1) * Wq - 1; tap0 = t * 3; }
+              else if (L.d.size == 3) {
+                const int kh = t / 3, kw = t % 3;
+                off = (long long)((kh & 1) * 2 + (kw & 1)) * L.plane_rows + (kh >> 1) * Wq + (kw >> 1);
+                tap0 = t;
+              }
+              if (off > 0x7fffffffLL - (1LL << 26)) { set_error("layer %d: batch too large for 32-bit row offsets", i); return AY_EINVAL; }
+              g.a_row_off[gi] = (int)off;
+              g.b_tap0[gi] = tap0;
+              // Small terms first: the tensor core adds into its fp32 accumulator with truncation, i.e. every MMA shrinks
+              // the running sum by about half an ulp OF THE SUM.  While only the two correction passes (2^-11 of the
+              // result) have been added that is negligible; the A_hi x W_hi pass comes last, so a third of the MMAs
+              // truncate at full magnitude instead of all of them.
+              g.a_col_off[gi] = pass == 0 ? L.cin : 0;              // pass 0: A_lo x W_hi
+              g.b_col_off[gi] = pass == 1 ? L.ktot : 0;             // pass 1: A_hi x W_lo; pass 2: A_hi x W_hi
+            }
+          (void)taps;
+          g.BN = L.BN; g.num_stages = L.stages; g.nbuf = L.nbuf; g.units_per_stage = 1;
+          g.tf32_na = ctx->tf32_na;
+          g.num_acc = std::min(16, 512 / (L.BN * g.tf32_na));
+          if (g.num_acc > 1) g.num_acc &= ~1;
+          g.dbg = ctx->dbg;
+          g.Hp = L.H + 2; g.Wp = Wq;
+          g.bias = L.bias; g.leaky = L.d.leaky; g.cout = L.C;
+          g.out_ptr = L.f_out; g.out_pitch = L.C;
+          g.err_flag = ctx->err_flag;
+          g.pdl = 0;
+          AY_TRY(ay::launch_conv_gemm(L.tmA, L.tmB, g, L.G, 2, ctx->num_sms, st));
+          ++ctx->launches;
+          break;
+        }
         ay::F32ConvParams q{};
         q.in = prev; q.in_pitch = pC; q.Cin = L.cin; q.H = pH; q.W = pW;
         q.w = L.f_w; q.bias = L.bias; q.Cout = L.C; q.size = L.d.size; q.stride = L.d.stride; q.leaky = L.d.leaky;

@@ -225,6 +225,53 @@ __global__ void f32_copy_channels_kernel(const float* __restrict__ in, int C, lo
   }
 }
 
+// Operand split for the tensor-core convolution of this mode (conv_gemm_sm100.cu, TF32): hi = v rounded to tf32
+// (10-bit mantissa, round to nearest, ties away), lo = v - hi, which is exact in fp32.  The MMA ignores the low 13
+// mantissa bits of its operands, so hi passes through unchanged and lo loses only its own 2^-11 tail: hi*W_hi + lo*W_hi
+// + hi*W_lo reproduces the fp32 product to ~2^-22 relative.  One row of C floats in, [hi | lo] = 2C floats out.
+__device__ __forceinline__ float tf32_round(float v) {
+  return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
+}
+__global__ void f32_split_kernel(const float4* __restrict__ in, int in_pitch4, int C4, long long rows,
+                                 float4* __restrict__ out) {
+  const long long total = rows * C4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / C4;
+    const int c = (int)(i - r * C4);
+    const float4 v = __ldg(in + r * in_pitch4 + c);
+    float4 h, l;
+    h.x = tf32_round(v.x); h.y = tf32_round(v.y); h.z = tf32_round(v.z); h.w = tf32_round(v.w);
+    l.x = __fsub_rn(v.x, h.x); l.y = __fsub_rn(v.y, h.y); l.z = __fsub_rn(v.z, h.z); l.w = __fsub_rn(v.w, h.w);
+    out[r * 2 * C4 + c] = h;
+    out[r * 2 * C4 + C4 + c] = l;
+  }
+}
+
+// Parity planes for the stride-2 tensor-core convolutions of this mode (classic one-pixel frame): plane pl = ph*2+pw,
+// position (a, b) of the output's padded grid holds padded input pixel (2(a-1)+ph, 2(b-1)+pw), zero outside.
+__global__ void f32_s2_gather_kernel(const float4* __restrict__ in, int P4, int batch, int H, int W,
+                                     float4* __restrict__ planes, long long plane_rows) {
+  const int Ho = H / 2, Wo = W / 2;
+  const int Hq = Ho + 2, Wq = Wo + 2, Hp = H + 2, Wp = W + 2;
+  const long long per_plane = (long long)batch * Hq * Wq * P4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < 4 * per_plane;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int pl = (int)(i / per_plane);
+    long long r = i - (long long)pl * per_plane;
+    const int c = (int)(r % P4);
+    r /= P4;
+    const int b = (int)(r % Wq);
+    r /= Wq;
+    const int a = (int)(r % Hq);
+    const int n = (int)(r / Hq);
+    const int iy = 2 * (a - 1) + (pl >> 1), ix = 2 * (b - 1) + (pl & 1);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (iy >= 0 && iy < Hp && ix >= 0 && ix < Wp) v = __ldg(in + ((size_t)((size_t)n * Hp + iy) * Wp + ix) * P4 + c);
+    planes[((size_t)pl * plane_rows + ((size_t)n * Hq + a) * Wq + b) * P4 + c] = v;
+  }
+}
+
 __global__ void f32_dump_nchw_kernel(const float* __restrict__ in, int C, int batch, int H, int W,
                                      float* __restrict__ out) {
   const long long total = (long long)batch * C * H * W;
@@ -284,6 +331,23 @@ int launch_f32_add(const float* a, const float* b, long long n, float* out, cuda
 
 int launch_f32_copy_channels(const float* in, int C, long long rows, float* out, int out_pitch, cudaStream_t s) {
   f32_copy_channels_kernel<<<grid_for32(rows * C), 256, 0, s>>>(in, C, rows, out, out_pitch);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_f32_split(const float* in, int in_pitch, int C, long long rows, float* out, cudaStream_t s) {
+  if ((C & 3) || (in_pitch & 3)) { set_error("f32 split: channels must be a multiple of 4"); return AY_EINVAL; }
+  f32_split_kernel<<<grid_for32(rows * (C / 4)), 256, 0, s>>>(reinterpret_cast<const float4*>(in), in_pitch / 4, C / 4, rows,
+                                                              reinterpret_cast<float4*>(out));
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_f32_s2_gather(const float* in, int pitch, int batch, int H, int W, float* planes, long long plane_rows,
+                         cudaStream_t s) {
+  const long long total = 4LL * batch * (H / 2 + 2) * (W / 2 + 2) * (pitch / 4);
+  f32_s2_gather_kernel<<<grid_for32(total), 256, 0, s>>>(reinterpret_cast<const float4*>(in), pitch / 4, batch, H, W,
+                                                         reinterpret_cast<float4*>(planes), plane_rows);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

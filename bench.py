@@ -61,6 +61,9 @@ def parse_args():
                    help="objectness bias of the synthetic checkpoint per head: a few dozen candidates per tile at conf 0.8, "
                         "mostly small boxes as in the reference's plaque data")
     p.add_argument("--cpu-sample", type=int, default=0, help="tiles in the bounded CPU-baseline sample")
+    p.add_argument("--precision", type=str, default="bf16", choices=["bf16", "fp32"],
+                   help="fp32: the accuracy mode (1e-4 bar) - 3 x tf32 on the tensor cores (dtype f32x3), or with AY_F32_FFMA=1 "
+                        "the CUDA-core FFMA kernel of round 1 (dtype f32-ffma)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true", help="device-resident value and roofline only (short runs under ncu)")
     args = p.parse_args()
@@ -450,6 +453,7 @@ def main():
     S = 416
     orig = (S, S) if args.config == "c2" else (args.tile, args.tile)
     cfg, model, sd = build_model(args.net, args.conf_bias)
+    model.precision = args.precision
     cap = 128
     det = TileDetector(model, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=B, cap=cap, device=dev)
     float_in = args.config == "c2"
@@ -646,7 +650,8 @@ def main():
         line = {
             "metric": METRIC, "value": world * B * K / (ms * 1e-3), "unit": "tiles/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic", "config": workload_config(args),
+            "dtype": "bf16" if args.precision == "bf16" else ("f32-ffma" if os.environ.get("AY_F32_FFMA") else "f32x3"),
+            "data": "synthetic", "config": workload_config(args),
             "gpu_launches": int(launches_per_step * K),
             "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
                        "samples": clk["samples"]},
@@ -658,6 +663,13 @@ def main():
                          "frac_of_burst": achieved / peaks["bf16_burst"]},
             "detections_per_step": n_det,
         }
+        if args.precision == "fp32":
+            # 3-pass tf32 at half the bf16 rate: the tensor ceiling of this mode is a sixth of the bf16 peak
+            line["roofline"]["peak"] = peaks["bf16"] / 6.0
+            line["roofline"]["frac"] = achieved / (peaks["bf16"] / 6.0)
+            line["roofline"]["peak_source"] += " / 6 (tf32 is half rate, three passes)"
+            line["roofline"]["kernel"] = "conv stack of the fp32 accuracy mode (ay_forward: %d launches)" % fwd_launches
+            line["config"]["workload"] += " [precision fp32: accuracy mode]"
         if e2e is not None:
             line["e2e"] = e2e
         if gather_verified is not None:

@@ -45,8 +45,9 @@ enum { AY_IN_F32_NCHW = 0,    /* [B,3,S,S] float, already /255 and resized (Dark
        AY_IN_U8_HWC   = 1 };  /* [B,H,W,3] uint8 tiles; ToTensor + nearest Resize (utils/transforms.py:89-111) fused into the first conv */
 
 /* activation storage type: AY_BF16 / AY_FP16 run the tcgen05 tensor-core path (2e-2 bar on the raw heads);
- * AY_F32 is the accuracy mode — fp32 storage and FFMA accumulation on the CUDA cores (1e-4 bar), one plain
- * kernel per cfg block, no fusion. */
+ * AY_F32 is the accuracy mode (1e-4 bar) — fp32 storage, one plain kernel per cfg block, no fusion; its convolutions
+ * run on the tensor cores as a 3-pass tf32 split (A_hi W_hi + A_lo W_hi + A_hi W_lo, fp32 accumulation in TMEM) where
+ * the channel counts are multiples of 32 and as an FFMA kernel on the CUDA cores elsewhere (first layer, heads). */
 enum { AY_BF16 = 0, AY_FP16 = 1, AY_F32 = 2 };
 
 typedef struct ay_layer_desc {
@@ -96,7 +97,7 @@ int  ay_net_layer_output(ay_ctx* ctx, int layer, int batch, float* out_nchw, voi
 int  ay_net_layer_shape(ay_ctx* ctx, int layer, int* channels, int* height, int* width);
 /* Which convolution implementation ran for `layer` in the last forward:
  * 0 = none, 1 = tcgen05 implicit GEMM, 2 = first-layer direct kernel, 3 = CUDA-core
- * cross-check over the 16-bit buffers, 4 = fp32 CUDA-core kernel (AY_F32 networks).  */
+ * cross-check over the 16-bit buffers, 4 = fp32 CUDA-core kernel, 5 = 3 x tf32 tcgen05 GEMM (AY_F32 networks).  */
 int  ay_net_layer_impl(ay_ctx* ctx, int layer);
 /* number of kernels one ay_forward launches for the built network                  */
 int  ay_net_launch_count(ay_ctx* ctx);

@@ -302,9 +302,9 @@ def test_forward_fp32_mode_mini_vs_reference_golden(golden, dev):
         y8 = eng.forward_u8(torch.from_numpy(g["tiles"])).cpu()                           # u8 / 255 + nearest resize
         eng.check()
         assert rel_max(y8, want) <= FP32_TOL
-        for i, dsc in enumerate(m.module_defs):
-            if dsc["type"] == "convolutional":
-                assert eng.layer_impl(i) == 4, "fp32 networks run the fp32 CUDA-core convolution"
+        impls = [eng.layer_impl(i) for i, dsc in enumerate(m.module_defs) if dsc["type"] == "convolutional"]
+        # 5 = 3 x tf32 on the tensor cores (channel counts multiples of 32), 4 = the fp32 CUDA-core kernel (first layer, heads)
+        assert set(impls) <= {4, 5} and impls[0] == 4 and impls.count(5) >= len(impls) - 4, impls
 
 
 @pytest.mark.parametrize("name,batch", [("yolov3-custom", 2), ("yolov3-tiny", 3)])
@@ -356,6 +356,24 @@ def test_forward_fp32_mode_full_networks_vs_oracle(name, batch, dev):
     # same tiles through the caller's float contract (Darknet.forward): identical bits to the u8 entry
     y = m(x)
     assert np.array_equal(bits(y), bits(got))
+    # the tensor-core convolutions (3 x tf32) against the CUDA-core FFMA kernel of round 1 on the same buffers
+    n_tc = sum(eng.layer_impl(i) == 5 for i in range(len(blocks) - 1))
+    assert n_tc >= 8
+    m._engine = None
+    os.environ["AY_F32_FFMA"] = "1"
+    try:
+        eng2 = m.engine(device=dev, max_batch=batch)
+        assert all(eng2.layer_impl(i) in (0, 4) for i in range(len(blocks) - 1))
+        ffma = eng2.forward_u8(torch.from_numpy(tiles)).cpu()
+        eng2.check()
+        for i, want in zip(heads, raw32):
+            a, b = eng.layer_output(i, batch).cpu(), eng2.layer_output(i, batch).cpu()
+            print("head %d: tf32x3 vs FFMA rel_max %.3e" % (i, rel_max(a, b)))
+            assert rel_max(a, b) <= FP32_TOL
+    finally:
+        del os.environ["AY_F32_FFMA"]
+        m._engine = None
+    assert rel_max(ffma, ref32) <= FP32_TOL
 
 
 def test_forward_batch_invariance_and_ragged_batches(dev):
