@@ -130,3 +130,90 @@ def non_max_suppression(prediction, conf_thres=0.5, nms_thres=0.4, return_keep=F
         output.append(rows_h[b, :k].clone() if k > 0 else None)
         kept.append(keep_h[b, :k].to(torch.int64) if k > 0 else None)
     return (output, kept) if return_keep else output
+
+
+# ----------------------------------------------------------------------------- evaluation statistics
+def xywh2xyxy_np(x):
+    """utils/utils.py:60-66."""
+    import numpy as np
+    y = np.zeros_like(x)
+    half_w, half_h = x[..., 2] / 2, x[..., 3] / 2
+    y[..., 0], y[..., 1] = x[..., 0] - half_w, x[..., 1] - half_h
+    y[..., 2], y[..., 3] = x[..., 0] + half_w, x[..., 1] + half_h
+    return y
+
+
+def compute_ap(recall, precision):
+    """Area under the precision envelope (utils/utils.py:123-149, py-faster-rcnn's AP): sentinels at both ends,
+    running maximum from the right, sum of (delta recall) * precision where recall changes."""
+    import numpy as np
+    mrec = np.concatenate(([0.0], recall, [1.0]))
+    mpre = np.concatenate(([0.0], precision, [0.0]))
+    mpre = np.maximum.accumulate(mpre[::-1])[::-1]
+    step = np.nonzero(mrec[1:] != mrec[:-1])[0]
+    return np.sum((mrec[step + 1] - mrec[step]) * mpre[step + 1])
+
+
+def ap_per_class(tp, conf, pred_cls, target_cls):
+    """utils/utils.py:69-120: per class present in ``target_cls`` -> (precision, recall, AP, F1, classes) with the
+    precision / recall of the LAST point of each curve, predictions ranked by descending ``conf``."""
+    import numpy as np
+    order = np.argsort(-conf)
+    tp, conf, pred_cls = tp[order], conf[order], pred_cls[order]
+    target_cls = np.asarray(target_cls)
+    classes = np.unique(target_cls)
+    ap, p, r = [], [], []
+    for c in classes:
+        mine = pred_cls == c
+        n_gt, n_p = (target_cls == c).sum(), mine.sum()
+        if n_p == 0 and n_gt == 0:
+            continue
+        if n_p == 0 or n_gt == 0:
+            ap.append(0), r.append(0), p.append(0)
+            continue
+        tpc = tp[mine].cumsum()
+        fpc = (1 - tp[mine]).cumsum()
+        recall_curve = tpc / (n_gt + 1e-16)
+        precision_curve = tpc / (tpc + fpc)
+        r.append(recall_curve[-1])
+        p.append(precision_curve[-1])
+        ap.append(compute_ap(recall_curve, precision_curve))
+    p, r, ap = np.array(p), np.array(r), np.array(ap)
+    f1 = 2 * p * r / (p + r + 1e-16)
+    return p, r, ap, f1, classes.astype("int32")
+
+
+def get_batch_statistics(outputs, targets, iou_threshold):
+    """utils/utils.py:152-190: per image with detections -> [true_positives, scores, labels].  A prediction (in NMS
+    order) is a true positive when its label occurs among the image's targets and its best-IoU target (first index on
+    ties, IoU >= iou_threshold) has not been claimed yet; the scan stops once every target is claimed.
+    ``outputs``: list of [k,7] tensors / None in network-input pixels; ``targets``: [n,6] (sample, class, x1,y1,x2,y2).
+    The IoUs of one image come from ONE ``ay_bbox_iou`` launch over all (prediction, target) pairs."""
+    import numpy as np
+    batch_metrics = []
+    for sample_i, output in enumerate(outputs):
+        if output is None:
+            continue
+        output = output.detach().cpu()
+        pred_boxes, pred_scores, pred_labels = output[:, :4], output[:, 4], output[:, -1]
+        true_positives = np.zeros(pred_boxes.shape[0])
+        annotations = targets[targets[:, 0] == sample_i][:, 1:]
+        if len(annotations):
+            target_labels = annotations[:, 0]
+            target_boxes = annotations[:, 1:].to(torch.float32)
+            n_p, n_t = pred_boxes.shape[0], target_boxes.shape[0]
+            iou = bbox_iou(pred_boxes.to(torch.float32).repeat_interleave(n_t, 0), target_boxes.repeat(n_p, 1)).view(n_p, n_t)
+            best_iou, best_idx = iou.max(1)
+            known = set(target_labels.tolist())
+            claimed = set()
+            for pred_i in range(n_p):
+                if len(claimed) == n_t:
+                    break
+                if float(pred_labels[pred_i]) not in known:
+                    continue
+                j = int(best_idx[pred_i])
+                if float(best_iou[pred_i]) >= iou_threshold and j not in claimed:
+                    true_positives[pred_i] = 1
+                    claimed.add(j)
+        batch_metrics.append([true_positives, pred_scores, pred_labels])
+    return batch_metrics

@@ -639,3 +639,75 @@ def merge_emulated(rows):
                     gone.append(b)
                     changed = True
     return np.asarray([list(e) for e in live.items()], dtype=f32).reshape(-1, 7)
+
+
+# --------------------------------------------------------------------------
+# evaluation statistics (utils/utils.py:69-190) - restated statement by statement
+# --------------------------------------------------------------------------
+
+
+def compute_ap_faithful(recall, precision):
+    """utils/utils.py:123-149."""
+    mrec = np.concatenate(([0.0], recall, [1.0]))
+    mpre = np.concatenate(([0.0], precision, [0.0]))
+    for i in range(mpre.size - 1, 0, -1):
+        mpre[i - 1] = np.maximum(mpre[i - 1], mpre[i])
+    i = np.where(mrec[1:] != mrec[:-1])[0]
+    return np.sum((mrec[i + 1] - mrec[i]) * mpre[i + 1])
+
+
+def ap_per_class_faithful(tp, conf, pred_cls, target_cls):
+    """utils/utils.py:69-120."""
+    i = np.argsort(-conf)
+    tp, conf, pred_cls = tp[i], conf[i], pred_cls[i]
+    unique_classes = np.unique(target_cls)
+    ap, p, r = [], [], []
+    for c in unique_classes:
+        i = pred_cls == c
+        n_gt = (target_cls == c).sum()
+        n_p = i.sum()
+        if n_p == 0 and n_gt == 0:
+            continue
+        elif n_p == 0 or n_gt == 0:
+            ap.append(0)
+            r.append(0)
+            p.append(0)
+        else:
+            fpc = (1 - tp[i]).cumsum()
+            tpc = (tp[i]).cumsum()
+            recall_curve = tpc / (n_gt + 1e-16)
+            r.append(recall_curve[-1])
+            precision_curve = tpc / (tpc + fpc)
+            p.append(precision_curve[-1])
+            ap.append(compute_ap_faithful(recall_curve, precision_curve))
+    p, r, ap = np.array(p), np.array(r), np.array(ap)
+    f1 = 2 * p * r / (p + r + 1e-16)
+    return p, r, ap, f1, unique_classes.astype("int32")
+
+
+def get_batch_statistics_faithful(outputs, targets, iou_threshold):
+    """utils/utils.py:152-190, with bbox_iou_xyxy (this file) in place of the reference's bbox_iou."""
+    batch_metrics = []
+    for sample_i in range(len(outputs)):
+        if outputs[sample_i] is None:
+            continue
+        output = np.asarray(outputs[sample_i], dtype=f32)
+        pred_boxes, pred_scores, pred_labels = output[:, :4], output[:, 4], output[:, -1]
+        true_positives = np.zeros(pred_boxes.shape[0])
+        annotations = targets[targets[:, 0] == sample_i][:, 1:]
+        target_labels = annotations[:, 0] if len(annotations) else []
+        if len(annotations):
+            detected_boxes = []
+            target_boxes = annotations[:, 1:].astype(f32)
+            for pred_i, (pred_box, pred_label) in enumerate(zip(pred_boxes, pred_labels)):
+                if len(detected_boxes) == len(annotations):
+                    break
+                if pred_label not in target_labels:
+                    continue
+                ious = bbox_iou_xyxy(pred_box, target_boxes)
+                box_index = int(np.argmax(ious))
+                if ious[box_index] >= iou_threshold and box_index not in detected_boxes:
+                    true_positives[pred_i] = 1
+                    detected_boxes += [box_index]
+        batch_metrics.append([true_positives, pred_scores, pred_labels])
+    return batch_metrics

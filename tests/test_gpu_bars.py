@@ -414,3 +414,94 @@ def test_head_epilogue_candidate_lists(name, conf_bias, thres, dev):
     _lib.check(lib.ay_forward_candidates(ctx, P(tiles), _lib.AY_IN_U8_HWC, B, 416, 416, P(dec), 1.5, P(idx), P(cnt), 8, st))
     eng.check()
     assert cnt.cpu().tolist() == [0, 0, 0]
+
+
+# ------------------------------------------------------------------ evaluation callers
+def test_get_batch_statistics_vs_reference_golden(golden):
+    """utils.get_batch_statistics (IoUs from one ay_bbox_iou launch per image) against the reference's outputs."""
+    from amyloid_yolo_paper_b200.utils.utils import get_batch_statistics
+    from oracle.make_golden_eval import stats_case
+    g = golden("eval_ref.npz")
+    n_tp = 0
+    for s in range(8):
+        outputs, targets = stats_case(s)
+        for thr in (0.5, 0.75):
+            m = get_batch_statistics(outputs, targets, thr)
+            assert len(m) == int(g["st_n_%d_%d" % (s, int(thr * 100))][0])
+            for i, (tp, sc, lb) in enumerate(m):
+                assert np.array_equal(tp, g["st_tp_%d_%d_%d" % (s, int(thr * 100), i)]), (s, thr, i)
+                assert np.array_equal(sc.numpy(), g["st_sc_%d_%d_%d" % (s, int(thr * 100), i)])
+                n_tp += int(tp.sum())
+    assert n_tp > 20
+
+
+def test_evaluate_and_prediction_dict(dev, tmp_path):
+    """test.evaluate (test.py:24-66) on PNG tiles + label files written here: (precision, recall, AP, f1, classes) equal
+    the oracle chain on the engine's own decoded tensor, with labels derived from the oracle's detections (so that true
+    and false positives both occur); and the prospective.py prediction dictionary has the reference's layout."""
+    from PIL import Image
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.models import Darknet
+    from amyloid_yolo_paper_b200.test import evaluate, run_model_on_validation_images
+    cfg = ensure_cfg("yolov3-custom")
+    m = Darknet(cfg)
+    sd = synth.planted_state_dict(m, seed=1)
+    tiles, _ = synth.planted_tiles(5, size=832, seed=4, objects=(6, 10))
+    (tmp_path / "images").mkdir()
+    (tmp_path / "labels").mkdir()
+    eng = m.engine(device=dev, max_batch=4)
+    dec = eng.forward_u8(torch.from_numpy(tiles)).cpu().numpy()
+    eng.check()
+    rng = np.random.default_rng(3)
+    files, want_metrics, all_labels = [], [], []
+    for b, t in enumerate(tiles):
+        f = str(tmp_path / "images" / ("t%d.png" % b))
+        Image.fromarray(t).save(f)
+        files.append(f)
+        rows, _ = R.nms_exact(dec[b], 0.8, 0.4)
+        # labels: most detections jittered by a few pixels (true positives), some with the other class, one stray box
+        lab = []
+        for r in rows[: max(1, len(rows) - 1)]:
+            cls = r[6] if rng.random() < 0.8 else 1 - r[6]
+            box = r[:4] + rng.normal(0, 2.0, 4)
+            lab.append([cls, (box[0] + box[2]) / 2 / 416, (box[1] + box[3]) / 2 / 416, (box[2] - box[0]) / 416, (box[3] - box[1]) / 416])
+        lab.append([0, 0.1, 0.1, 0.05, 0.05])
+        lab = np.clip(np.array(lab, dtype=np.float64), 0, 1)
+        np.savetxt(str(tmp_path / "labels" / ("t%d.txt" % b)), lab, fmt="%.6f")
+    (tmp_path / "list.txt").write_text("\n".join(files) + "\n")
+    got = evaluate(m, str(tmp_path / "list.txt"), iou_thres=0.5, conf_thres=0.8, nms_thres=0.4, img_size=416, batch_size=4)
+    # oracle: the same list walk on the engine's decoded tensor
+    from amyloid_yolo_paper_b200.test import _load_labels
+    for b0 in range(0, 5, 4):
+        outs, tg = [], []
+        for i, b in enumerate(range(b0, min(5, b0 + 4))):
+            rows, _ = R.nms_exact(dec[b], 0.8, 0.4)
+            outs.append(rows)
+            boxes = _load_labels(files[b]).astype(np.float32)
+            t = np.zeros((len(boxes), 6), np.float32)
+            t[:, 0], t[:, 1] = i, boxes[:, 0]
+            t[:, 2:] = R.xywh2xyxy(boxes[:, 1:]) * np.float32(416)
+            tg.append(t)
+            all_labels += boxes[:, 0].tolist()
+        want_metrics += R.get_batch_statistics_faithful(outs, np.concatenate(tg, 0), 0.5)
+    tp, sc, lb = [np.concatenate(x, 0) for x in zip(*want_metrics)]
+    want = R.ap_per_class_faithful(tp, sc, lb, np.asarray(all_labels))
+    assert got is not None
+    for a, b in zip(got, want):
+        assert np.array_equal(np.asarray(a), np.asarray(b))
+    assert 0 < tp.sum() < len(tp) and got[2].max() > 0.3
+    # prediction dictionary (prospective.py:84-92)
+    preds = run_model_on_validation_images(m, str(tmp_path / "images") + "/", ["CAA", "Cored"], batch_size=2, n_cpu=2)
+    assert sorted(preds) == ["t%d.png" % b for b in range(5)]
+    n = 0
+    for b in range(5):
+        want_rows = _oracle_final(dec[b], 416, (832, 832))
+        entries = preds["t%d.png" % b]
+        assert len(entries) == len(want_rows)
+        for (d, name), w in zip(entries, want_rows):
+            assert set(d) == {"x1", "x2", "y1", "y2", "conf", "cls_conf", "cls_pred"}
+            assert [np.float32(d[k]) for k in ("x1", "y1", "x2", "y2", "conf", "cls_conf", "cls_pred")] == list(w)
+            assert name == ["CAA", "Cored"][int(w[6])]
+            n += 1
+    assert n > 10

@@ -186,3 +186,25 @@ def test_preprocess_vs_reference_golden(golden):
     want = g["sample_rows"]                                                # [3,8,416] fp32
     got = (torch.from_numpy(src).permute(2, 0, 1).float() / 255).numpy()
     assert np.array_equal(bits(got), bits(want))
+
+
+def test_evaluation_statistics_vs_reference_golden(golden):
+    """ap_per_class / compute_ap (product, host numpy - as in the reference) and the oracle's restatement against the
+    reference's outputs (utils/utils.py:69-149), and the oracle's get_batch_statistics against utils/utils.py:152-190."""
+    from amyloid_yolo_paper_b200.utils.utils import ap_per_class
+    from oracle.make_golden_eval import eval_case, stats_case
+    g = golden("eval_ref.npz")
+    for s in range(12):
+        tp, conf, pred_cls, target_cls = eval_case(s)
+        for fn in (ap_per_class, R.ap_per_class_faithful):
+            p, r, ap, f1, cls = fn(tp.copy(), conf.copy(), pred_cls.copy(), np.asarray(target_cls))
+            assert np.array_equal(cls, g["ap_cls_%d" % s])
+            for name, v in (("p", p), ("r", r), ("ap", ap), ("f1", f1)):
+                assert np.array_equal(v, g["ap_%s_%d" % (name, s)]), (fn.__name__, s, name)
+    for s in range(8):
+        outputs, targets = stats_case(s)
+        for thr in (0.5, 0.75):
+            m = R.get_batch_statistics_faithful([o.numpy() if o is not None else None for o in outputs], targets.numpy(), thr)
+            assert len(m) == int(g["st_n_%d_%d" % (s, int(thr * 100))][0])
+            for i, (tp, sc, lb) in enumerate(m):
+                assert np.array_equal(tp, g["st_tp_%d_%d_%d" % (s, int(thr * 100), i)])
