@@ -96,6 +96,9 @@ _PROTOTYPES = {
     "ay_nms_timed": [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float,
                      ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                      ctypes.POINTER(ctypes.c_float)],
+    "ay_nms_static_capacity": [],
+    "ay_nms_static": [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_float,
+                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p],
     "ay_rescale_merge": [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                          ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
                          ctypes.c_void_p, ctypes.c_void_p],
@@ -128,6 +131,7 @@ def load():
             fn = getattr(lib, name)
             fn.argtypes = args
             fn.restype = ctypes.c_int
+        lib.ay_nms_static_capacity.restype = ctypes.c_size_t
         lib.ay_last_error.argtypes = []
         lib.ay_last_error.restype = ctypes.c_char_p
         _lib = lib

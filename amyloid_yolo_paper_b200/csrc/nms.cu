@@ -19,6 +19,8 @@
 //   cluster : one warp per keeper: ordered member list, ATen-order weighted sums
 #include "ay_common.h"
 
+#include <mutex>
+
 namespace ay {
 namespace {
 
@@ -444,4 +446,74 @@ int launch_bbox_iou(const float* b1, int n1, const float* b2, int n2, float* out
   return AY_OK;
 }
 
+// ------------------------------------------------------------------ ay_nms_static
+// The allocation-free variant of ay_nms: the scratch of the four kernels lives in one file-scope device array instead
+// of a cudaMalloc'd, context-owned buffer.  Every GPU that loads the library holds these kStaticScratchBytes until the
+// process exits.  The first 256 bytes hold the overflow flag of nms_cluster_kernel, the NMS carve-up follows.
+constexpr size_t kStaticFlagBytes = 256;
+constexpr size_t kStaticScratchBytes = (size_t)32 << 20;   // 32 MiB: 2 tiles x 10 647 rows (416^2), 36 x 2 535 (tiny)
+constexpr int kStaticMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_nms_static_scratch[kStaticScratchBytes];
+
+// In host code the array's name is only a handle: the device address is looked up once per device, with that device
+// current, and it is this pointer that the kernels receive.
+static int static_scratch_address(uint8_t** out) {
+  static uint8_t* addr[kStaticMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  AY_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kStaticMaxDevices) {
+    set_error("ay_nms_static: device ordinal %d outside [0, %d)", dev, kStaticMaxDevices);
+    return AY_EINVAL;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* ptr = nullptr;
+    AY_CUDA(cudaGetSymbolAddress(&ptr, g_nms_static_scratch));
+    if (!ptr) {
+      set_error("ay_nms_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+      return AY_ECUDA;
+    }
+    addr[dev] = static_cast<uint8_t*>(ptr);
+  }
+  *out = addr[dev];
+  return AY_OK;
+}
+
 }  // namespace ay
+
+extern "C" size_t ay_nms_static_capacity(void) { return ay::kStaticScratchBytes - ay::kStaticFlagBytes; }
+
+extern "C" int ay_nms_static(float* pred, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres,
+                             float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream) {
+  using namespace ay;
+  if (!pred || !out_rows || !out_keep || !out_counts || batch < 1 || n_rows < 1) {
+    set_error("ay_nms_static: bad arguments");
+    return AY_EINVAL;
+  }
+  if (n_rows > kMaxRows) {
+    set_error("ay_nms_static: %d rows per tile exceed the on-chip sort capacity of %d", n_rows, kMaxRows);
+    return AY_EINVAL;
+  }
+  // in 64-bit arithmetic before make_layout: the IoU bit matrix grows with batch * n_rows^2
+  const unsigned long long mask_bytes = 8ull * (unsigned long long)batch * (unsigned long long)n_rows *
+                                        (unsigned long long)((n_rows + 63) / 64);
+  const size_t room = kStaticScratchBytes - kStaticFlagBytes;
+  const size_t need = mask_bytes > room ? (size_t)mask_bytes : nms_scratch_bytes(batch, n_rows);
+  if (need > room) {
+    set_error("ay_nms_static: %d tiles x %d rows need %zu bytes of scratch, the static array holds %zu "
+              "(use ay_nms, whose scratch is allocated to size)", batch, n_rows, need, room);
+    return AY_ECAPACITY;
+  }
+  uint8_t* base = nullptr;
+  int rc = static_scratch_address(&base);
+  if (rc != AY_OK) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  unsigned int* flag = reinterpret_cast<unsigned int*>(base);
+  // the array keeps the previous call's contents: only the flag has to start at zero, the kernels write every other
+  // word of the carve-up before they read it
+  AY_CUDA(cudaMemsetAsync(flag, 0, kStaticFlagBytes, s));
+  return launch_nms(pred, batch, n_rows, n_classes, conf_thres, nms_thres, out_rows, out_keep, out_counts, cap,
+                    base + kStaticFlagBytes, room, flag, s);
+}

@@ -22,6 +22,7 @@
 #ifndef AMYLOID_YOLO_H_
 #define AMYLOID_YOLO_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -133,6 +134,19 @@ int  ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* counts, int
 /* bbox_iou (utils/utils.py:202-232, x1y1x2y2=True): iou[i] of box1[i or 0] vs box2[i]. */
 int  ay_bbox_iou(ay_ctx* ctx, const float* box1, int n1, const float* box2, int n2,
                  float* out_iou, void* stream);
+/* ay_nms without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments and results as ay_nms (bit-identical; `pred` is rewritten to xyxy in place), but no context: it runs on
+ * the CURRENT device, and the scratch of its four kernels is one file-scope `static __device__` array of 32 MiB
+ * (csrc/nms.cu) that every GPU loading the library holds until the process exits.  ay_nms_static_capacity() returns
+ * the usable bytes: 2 tiles x 10 647 rows (yolov3 at 416^2), 9 tiles x 6 300 rows (320^2), 36 tiles x 2 535 rows
+ * (yolov3-tiny).  A larger batch x n_rows is rejected with AY_ECAPACITY before anything is launched.  It calls no
+ * cudaMalloc / cudaFree / allocating library routine.  All calls share the array: two calls that overlap on one GPU
+ * (different streams or threads) race - serialise them.  With no context there is no ay_check(): a tile with more
+ * than `cap` kept boxes reports out_counts[b] = -1 (cap >= n_rows cannot overflow).                    */
+size_t ay_nms_static_capacity(void);
+int  ay_nms_static(float* pred, int batch, int n_rows, int n_classes, float conf_thres, float nms_thres,
+                   float* out_rows, int32_t* out_keep, int32_t* out_counts, int cap, void* stream);
 /* Synchronise `stream` and report asynchronous errors / capacity overflows.         */
 int  ay_check(ay_ctx* ctx, void* stream);
 
