@@ -8,6 +8,7 @@
 //   dump_nchw       test helper: padded NHWC 16-bit -> NCHW fp32
 //   ref_conv        CUDA-core direct convolution, test cross-check of the tcgen05 kernel
 //   decode          stand-alone YOLO decode (models.py:137-169) used with ref_conv
+//   linear          fully connected output layer of the CAA filter network (core.py:161-205)
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -93,7 +94,7 @@ __global__ void first_conv_kernel(FirstConvParams p) {
 #pragma unroll
         for (int k = 0; k < 27; ++k) a = fmaf(in[k], w[k], a);
         a += sw[nw + oc];
-        if (p.leaky) a = a > 0.f ? a : 0.1f * a;
+        if (p.leaky) a = a > 0.f ? a : act_slope(p.leaky) * a;
       }
       acc[j] = a;
     }
@@ -299,7 +300,7 @@ __global__ void ref_conv_kernel(RefConvParams p) {
             acc = fmaf(ld16(p.in, irow * p.in_pitch + c, p.is_fp16), ld16(p.w, wrow + c, p.is_fp16), acc);
         }
       acc += p.bias[oc];
-      if (p.leaky) acc = acc > 0.f ? acc : 0.1f * acc;
+      if (p.leaky) acc = acc > 0.f ? acc : act_slope(p.leaky) * acc;
       if (p.residual) acc += ld16(p.residual, (size_t)m * p.res_pitch + oc, p.is_fp16);
     }
     if (p.raw_f32) p.raw_f32[(size_t)m * p.cout_p + oc] = acc;
@@ -423,6 +424,44 @@ int launch_dump_planes_nchw(const void* planes, long long plane_rows, int pitch,
 int launch_ref_conv(const RefConvParams& p, cudaStream_t s) {
   const long long total = (long long)p.batch * padded(p.Ho) * padded(p.Wo) * p.cout_p;
   ref_conv_kernel<<<grid_for(total), 256, 0, s>>>(p);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+// ---------------------------------------------------------------- fully connected output layer (AY_LINEAR)
+// out[b, o] = bias[o] + sum_{y,x,c} act[b, y, x, c] * w[o, (y*W + x)*C + c]   (core.py:161-205: x.view(B, -1) + nn.Linear,
+// the weight columns reordered from (c, y, x) to (y, x, c) by ay_net_set_conv).  One block per (tile, output); the
+// activation is a zero-haloed NHWC tensor of 16-bit (elem_bytes 2) or fp32 (4) elements with `lo` halo pixels before
+// and `hi` after every row / image.  A few thousand multiply-adds per output: the time of a 6 KB read, not a GEMM.
+namespace {
+__global__ void __launch_bounds__(128)
+linear_kernel(const void* __restrict__ act, int elem_bytes, int is_fp16, int pitch, int lo, int hi, int C, int H, int W,
+              const float* __restrict__ w, const float* __restrict__ bias, int O, float* __restrict__ out) {
+  const int b = blockIdx.y, o = blockIdx.x;
+  const int Hp = H + lo + hi, Wp = W + lo + hi;
+  const int n = H * W * C;
+  const float* wr = w + (size_t)o * n;
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int c = i % C, px = i / C;
+    const int y = px / W, x = px - y * W;
+    const size_t row = ((size_t)b * Hp + y + lo) * Wp + x + lo;
+    const float a = elem_bytes == 4 ? static_cast<const float*>(act)[row * pitch + c] : ld16(act, row * pitch + c, is_fp16);
+    acc = fmaf(a, wr[i], acc);
+  }
+  __shared__ float part[4];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) out[(size_t)b * O + o] = ((part[0] + part[1]) + (part[2] + part[3])) + bias[o];
+}
+}  // namespace
+
+int launch_linear(const void* act, int elem_bytes, int is_fp16, int pitch, int lo, int hi, int batch, int C, int H, int W,
+                  const float* w, const float* bias, int O, float* out, cudaStream_t s) {
+  if (batch < 1 || O < 1 || C < 1 || H < 1 || W < 1) { set_error("linear: bad shape"); return AY_EINVAL; }
+  linear_kernel<<<dim3(O, batch), 128, 0, s>>>(act, elem_bytes, is_fp16, pitch, lo, hi, C, H, W, w, bias, O, out);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

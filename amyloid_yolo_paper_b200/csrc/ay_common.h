@@ -13,6 +13,9 @@ namespace ay {
 
 void set_error(const char* fmt, ...);
 
+// negative-side slope of a convolution's activation (ay_layer_desc.leaky): 1 LeakyReLU(0.1), 2 ReLU
+__host__ __device__ inline float act_slope(int leaky) { return leaky == 2 ? 0.0f : 0.1f; }
+
 #define AY_CUDA(expr)                                                                     \
   do {                                                                                    \
     cudaError_t _e = (expr);                                                              \
@@ -173,6 +176,10 @@ struct DecodeParams {
   int lo, hi;            // zero pixels before / after each row and column of `raw`'s padded grid
 };
 int launch_decode(const DecodeParams& p, cudaStream_t s);
+// fully connected output layer over a zero-haloed NHWC activation (16-bit: elem_bytes 2, fp32: 4); w [O][H*W*C] in
+// (y, x, c) order, out [batch][O]
+int launch_linear(const void* act, int elem_bytes, int is_fp16, int pitch, int lo, int hi, int batch, int C, int H, int W,
+                  const float* w, const float* bias, int O, float* out, cudaStream_t s);
 
 // fp32_path.cu (act_dtype = AY_F32: fp32 storage, CUDA-core FFMA accumulation) ------------------
 struct F32PrepParams {

@@ -616,7 +616,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
               float y = __fadd_rn(__uint_as_float(v[e]), bias[e]);
-              if (p.leaky) y = y > 0.f ? y : __fmul_rn(y, 0.1f);
+              if (p.leaky) y = y > 0.f ? y : __fmul_rn(y, act_slope(p.leaky));
               v[e] = __float_as_uint(y);
             }
             if (store && !(p.dbg & 4)) {
@@ -731,9 +731,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               f[2 * q + 1] = add2(make_float2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])), make_float2(bb.z, bb.w));
             }
             if (p.leaky) {
+              const float slope = act_slope(p.leaky);            // 0.1 LeakyReLU, 0 ReLU
 #pragma unroll
-              for (int e = 0; e < 16; ++e) {                     // max(x, 0.1x) == (x > 0 ? x : 0.1x) for every x
-                const float2 s = mul2(f[e], make_float2(0.1f, 0.1f));
+              for (int e = 0; e < 16; ++e) {                     // max(x, s*x) == (x > 0 ? x : s*x) for every x, 0 <= s < 1
+                const float2 s = mul2(f[e], make_float2(slope, slope));
                 f[e].x = fmaxf(f[e].x, s.x);
                 f[e].y = fmaxf(f[e].y, s.y);
               }

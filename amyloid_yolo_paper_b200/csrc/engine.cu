@@ -146,6 +146,8 @@ struct Layer {
   // fp32 accuracy mode (AY_F32, fp32_path.cu): zero-haloed NHWC fp32 rows, pitch = C; weights [K][Cout]
   float* f_out = nullptr;
   float* f_w = nullptr;
+  float* lin_w32 = nullptr;         // AY_LINEAR: [filters][H*W*C] fp32, columns in (y, x, c) order
+  int lin_c = 0, lin_h = 0, lin_w = 0;   // AY_LINEAR: shape of the block it flattens
   float* f_w2 = nullptr;            // tensor-core variant (impl 5): [Cout][2 * taps * Cin] = [W_hi | W_lo], K order (tap, c)
 };
 
@@ -422,13 +424,24 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
         L.C = pc; L.H = ph; L.W = pw;
         break;
       }
+      case AY_LINEAR: {
+        if (i == 0 || i != n_layers - 1 || d.filters < 1 || ctx->dec_rows != 0) {
+          set_error("layer %d: a fully connected layer must be the last block of a network without [yolo] blocks", i);
+          return AY_EINVAL;
+        }
+        L.lin_c = pc; L.lin_h = ph; L.lin_w = pw;
+        ctx->dec_rows = 1;
+        ctx->dec_cols = d.filters;
+        L.C = d.filters; L.H = 1; L.W = 1;
+        break;
+      }
       default:
         set_error("layer %d: unknown type %d", i, d.type);
         return AY_EINVAL;
     }
     pc = L.C; ph = L.H; pw = L.W;
   }
-  if (ctx->dec_rows == 0) { set_error("network has no [yolo] block"); return AY_EINVAL; }
+  if (ctx->dec_rows == 0) { set_error("network has no [yolo] block and no fully connected output layer"); return AY_EINVAL; }
 
   // ---- fp32 accuracy mode: one buffer per block, no fusion
   if (ctx->is_f32) {
@@ -476,6 +489,10 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
           break;
         case AY_YOLO:
           L.f_out = Ls[i - 1].f_out;
+          break;
+        case AY_LINEAR:
+          AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.lin_w32), sizeof(float) * (size_t)L.C * L.lin_c * L.lin_h * L.lin_w, true));
+          AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.C, true));
           break;
         default:
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_out), sizeof(float) * elems, true));
@@ -713,6 +730,12 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.raw_f32),
                            sizeof(float) * (size_t)ay::padded_rows(max_batch, L.H, L.W) * L.cout_rows, true));
   }
+  if (Ls[n_layers - 1].d.type == AY_LINEAR) {
+    Layer& L = Ls[n_layers - 1];
+    if (!Ls[n_layers - 2].out.ptr) { set_error("layer %d: input of the fully connected layer is not materialised", n_layers - 1); return AY_EINVAL; }
+    AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.lin_w32), sizeof(float) * (size_t)L.C * L.lin_c * L.lin_h * L.lin_w, true));
+    AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.C, true));
+  }
   AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_y), sizeof(int) * img_size, true));
   AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&ctx->idx_x), sizeof(int) * img_size, true));
   AY_CUDA(cudaDeviceSynchronize());
@@ -722,11 +745,24 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
 
 extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const float* bias) {
   AY_ENTER(ctx);
-  if (!ctx->built || layer < 0 || layer >= (int)ctx->layers.size() || ctx->layers[layer].d.type != AY_CONV || !w || !bias) {
+  if (!ctx->built || layer < 0 || layer >= (int)ctx->layers.size() || (ctx->layers[layer].d.type != AY_CONV && ctx->layers[layer].d.type != AY_LINEAR) || !w || !bias) {
     set_error("ay_net_set_conv: bad layer %d", layer);
     return AY_EINVAL;
   }
   Layer& L = ctx->layers[layer];
+  if (L.d.type == AY_LINEAR) {
+    // nn.Linear weight [O][C*H*W] over x.view(B, -1) of an NCHW tensor (core.py:203-204) -> columns in (y, x, c) order
+    const int C = L.lin_c, HW = L.lin_h * L.lin_w;
+    std::vector<float> r((size_t)L.C * C * HW);
+    for (int o = 0; o < L.C; ++o)
+      for (int c = 0; c < C; ++c)
+        for (int px = 0; px < HW; ++px) r[((size_t)o * HW + px) * C + c] = w[((size_t)o * C + c) * HW + px];
+    AY_CUDA(cudaMemcpy(L.lin_w32, r.data(), r.size() * sizeof(float), cudaMemcpyHostToDevice));
+    AY_CUDA(cudaMemcpy(L.bias, bias, sizeof(float) * L.C, cudaMemcpyHostToDevice));
+    L.weights_set = true;
+    ctx->finalized = false;
+    return AY_OK;
+  }
   const int k = L.d.size, taps = k * k, cout = L.C, cin = L.cin;
   if (ctx->is_f32) {
     std::vector<float> r((size_t)taps * cin * cout);          // OIHW -> [(kh,kw,c)][o]
@@ -831,7 +867,7 @@ extern "C" int ay_net_finalize(ay_ctx* ctx) {
   AY_ENTER(ctx);
   if (!ctx->built) { set_error("ay_net_finalize before ay_net_build"); return AY_ESTATE; }
   for (size_t i = 0; i < ctx->layers.size(); ++i)
-    if (ctx->layers[i].d.type == AY_CONV && !ctx->layers[i].weights_set) {
+    if ((ctx->layers[i].d.type == AY_CONV || ctx->layers[i].d.type == AY_LINEAR) && !ctx->layers[i].weights_set) {
       set_error("layer %zu has no weights", i);
       return AY_ESTATE;
     }
@@ -995,6 +1031,10 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
         ++ctx->launches;
         break;
       }
+      case AY_LINEAR:
+        AY_TRY(ay::launch_linear(prev, 4, 0, pC, 1, 1, batch, L.lin_c, L.lin_h, L.lin_w, L.lin_w32, L.bias, L.C, dec_out, st));
+        ++ctx->launches;
+        break;
       default:
         break;
     }
@@ -1216,6 +1256,13 @@ extern "C" int ay_forward(ay_ctx* ctx, const void* input, int in_kind, int batch
           ++ctx->launches;
         }
         break;
+      case AY_LINEAR: {
+        const ActView& in = Ls[i - 1].out;
+        AY_TRY(ay::launch_linear(in.ptr, 2, ctx->is_fp16, in.pitch, ay::kPadLo, 1, batch, L.lin_c, L.lin_h, L.lin_w, L.lin_w32,
+                                 L.bias, L.C, out_decoded, st));
+        ++ctx->launches;
+        break;
+      }
       case AY_SHORTCUT:
         if (!L.fused_into_prev) {
           const ActView& a = Ls[i - 1].out;

@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(256) f32_conv_kernel(F32ConvParams p) {
       const int c = n0 + tx * 4 + j;
       if (c >= p.Cout) continue;
       float v = __fadd_rn(acc[i][j], __ldg(p.bias + c));
-      if (p.leaky) v = v > 0.f ? v : __fmul_rn(v, 0.1f);
+      if (p.leaky) v = v > 0.f ? v : __fmul_rn(v, act_slope(p.leaky));
       o[c] = v;
     }
   }

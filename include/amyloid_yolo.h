@@ -39,7 +39,10 @@ extern "C" {
 typedef struct ay_ctx ay_ctx;
 
 /* layer kinds, one per cfg block type handled by models.py:16-83 */
-enum { AY_CONV = 0, AY_MAXPOOL = 1, AY_UPSAMPLE = 2, AY_ROUTE = 3, AY_SHORTCUT = 4, AY_YOLO = 5 };
+enum { AY_CONV = 0, AY_MAXPOOL = 1, AY_UPSAMPLE = 2, AY_ROUTE = 3, AY_SHORTCUT = 4, AY_YOLO = 5,
+       AY_LINEAR = 6 };      /* fully connected OUTPUT layer over the flattened previous block (core.py:199-205, the
+                              * CAA filter network): `filters` outputs; a network ends in [yolo] blocks or in one
+                              * AY_LINEAR, whose [B, filters] fp32 result is what ay_forward writes to out_decoded */
 
 /* input kinds accepted by ay_forward */
 enum { AY_IN_F32_NCHW = 0,    /* [B,3,S,S] float, already /255 and resized (Darknet.forward contract) */
@@ -56,7 +59,7 @@ typedef struct ay_layer_desc {
   int32_t filters;          /* conv: output channels                                    */
   int32_t size;             /* conv / maxpool: kernel size (conv pad = (size-1)/2)      */
   int32_t stride;           /* conv / maxpool / upsample                                */
-  int32_t leaky;            /* conv: 1 = LeakyReLU(0.1) after bias, 0 = linear          */
+  int32_t leaky;            /* conv: after bias 0 = linear, 1 = LeakyReLU(0.1), 2 = ReLU */
   int32_t n_src;            /* route: number of sources; shortcut: 1                    */
   int32_t src[4];           /* ABSOLUTE layer indices (route layers / shortcut from)    */
   int32_t n_anchors;        /* yolo                                                     */
@@ -76,7 +79,8 @@ int  ay_net_build(ay_ctx* ctx, const ay_layer_desc* layers_h, int n_layers,
                   int in_channels, int img_size, int max_batch, int act_dtype);
 /* Weights of conv layer `layer` (index into layers_h): OIHW fp32 with BatchNorm
  * already folded by the caller (w' = w*gamma/sqrt(var+eps), b' = beta-mean*gamma/sqrt(var+eps)),
- * bias_h has `filters` entries.  Synchronous (host buffers may be freed on return). */
+ * bias_h has `filters` entries.  For an AY_LINEAR layer: nn.Linear's weight [filters][C*H*W] over the flattened NCHW
+ * block (core.py:203-204) and its bias.  Synchronous (host buffers may be freed on return). */
 int  ay_net_set_conv(ay_ctx* ctx, int layer, const float* w_oihw_h, const float* bias_h);
 int  ay_net_finalize(ay_ctx* ctx);
 /* rows (sum A*G*G) and columns (5+C) of the decoded output per tile                */

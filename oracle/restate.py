@@ -711,3 +711,87 @@ def get_batch_statistics_faithful(outputs, targets, iou_threshold):
                     detected_boxes += [box_index]
         batch_metrics.append([true_positives, pred_scores, pred_labels])
     return batch_metrics
+
+
+# --------------------------------------------------------------------------
+# consensus CAA filter: core.py:109-159 get256Img, 161-205 Net, 210-221 getClassPreds,
+# 425-452 filterDetectionsByCAAModel
+# --------------------------------------------------------------------------
+CAA_CHANNELS = (3, 16, 32, 48, 64, 80, 96)
+
+
+def caa_net_forward(state, x, dtype=torch.float64):
+    """core.py:165-205 in eval mode: six (Conv2d 3x3 pad 1, BatchNorm2d, ReLU, MaxPool2d 2/2) stages on a
+    [B,3,256,256] tensor, flatten in NCHW order, one Linear(96*4*4, 3).  ``state`` uses the reference's
+    state_dict names (features.{4k}.weight/bias, features.{4k+1}.*, classifier.0.*).  Returns the LOGITS."""
+    y = x.to(dtype)
+    for k in range(6):
+        c, b = "features.%d." % (4 * k), "features.%d." % (4 * k + 1)
+        y = F.conv2d(y, state[c + "weight"].to(dtype), state[c + "bias"].to(dtype), padding=1)
+        y = F.batch_norm(y, state[b + "running_mean"].to(dtype), state[b + "running_var"].to(dtype),
+                         state[b + "weight"].to(dtype), state[b + "bias"].to(dtype), False, 0.0, 1e-5)
+        y = F.max_pool2d(F.relu(y), 2, 2)
+    y = y.reshape(y.shape[0], -1)
+    return F.linear(y, state["classifier.0.weight"].to(dtype), state["classifier.0.bias"].to(dtype))
+
+
+def get256img_box_faithful(bbox_coord, size=1536):
+    """core.py:109-159: the crop window (x_left, x_right, y_top, y_bottom) the reference slices for a box
+    (top-left x, top-left y, width, height).  Same branch order, including its quirks: the comparisons are strict,
+    later ``if``s overwrite earlier ones, and a window that no branch sets stays (-1, -1, -1, -1)."""
+    cx = int(bbox_coord[0] + (bbox_coord[2] / 2))
+    cy = int(bbox_coord[1] + (bbox_coord[3] / 2))
+    x_left_valid, x_right_valid = cx - 128 > 0, cx + 128 < size
+    y_top_valid, y_bottom_valid = cy - 128 > 0, cy + 128 < size
+    x_valid, y_valid = x_left_valid and x_right_valid, y_top_valid and y_bottom_valid
+    xl, xr, yt, yb = -1, -1, -1, -1
+    if x_valid and y_valid:
+        xl, xr, yt, yb = cx - 128, cx + 128, cy - 128, cy + 128
+    elif x_valid and not y_valid:
+        if y_bottom_valid:
+            xl, xr, yt, yb = cx - 128, cx + 128, 0, 256
+        if y_top_valid:
+            xl, xr, yt, yb = cx - 128, cx + 128, size - 256, size
+    elif not x_valid and y_valid:
+        if x_left_valid:
+            xl, xr, yt, yb = size - 256, size, cy - 128, cy + 128
+        if x_right_valid:
+            xl, xr, yt, yb = 0, 256, cy - 128, cy + 128
+    else:
+        if x_right_valid and y_bottom_valid:
+            xl, xr, yt, yb = 0, 256, 0, 256
+        if x_left_valid and y_bottom_valid:
+            xl, xr, yt, yb = size - 256, size, 0, 256
+        if x_right_valid and y_top_valid:
+            xl, xr, yt, yb = 0, 256, size - 256, size
+        if x_left_valid and y_top_valid:
+            xl, xr, yt, yb = size - 256, size, size - 256, size
+    return xl, xr, yt, yb
+
+
+def caa_normalise(crop_rgb_u8, mean, std):
+    """core.py:214-217: ToTensor (/255, HWC -> CHW) + Normalize(mean, std) in fp32, as torchvision computes them."""
+    t = torch.from_numpy(np.ascontiguousarray(crop_rgb_u8)).permute(2, 0, 1).to(torch.float32).div(255)
+    m = torch.as_tensor(mean, dtype=torch.float32).view(-1, 1, 1)
+    s = torch.as_tensor(std, dtype=torch.float32).view(-1, 1, 1)
+    return t.sub(m).div(s)
+
+
+def caa_filter_faithful(img_rgb_u8, detections, classes, state, mean, std, dtype=torch.float64, return_logits=False):
+    """core.py:425-452 on an in-memory tile (``img_rgb_u8`` = cv2.imread + the BGR->RGB swap of core.py:214):
+    detections [n,7] -> set of row tuples -> per box a 256^2 crop centred on it -> sigmoid(Net) -> CAA boxes with
+    CAA_pred <= 0.5 are dropped.  Row order is the set's iteration order, as in the reference.  Returns an [m,7]
+    float64-valued list of rows (and, on request, the CAA logit of every distinct row, in that order)."""
+    rows = [tuple(r) for r in np.asarray(detections).tolist()]
+    kept, logits = [], []
+    for x1, y1, x2, y2, conf, cls_conf, cls_pred in set(rows):
+        xl, xr, yt, yb = get256img_box_faithful((int(x1), int(y1), int(x2 - x1), int(y2 - y1)), img_rgb_u8.shape[0])
+        crop = img_rgb_u8[yt:yb, xl:xr]
+        with torch.no_grad():
+            out = caa_net_forward(state, caa_normalise(crop, mean, std).unsqueeze(0), dtype)[0]
+        caa_pred = float(torch.sigmoid(out[2]))
+        logits.append(float(out[2]))
+        if classes[int(cls_pred)] == "CAA" and caa_pred <= 0.5:
+            continue
+        kept.append((x1, y1, x2, y2, conf, cls_conf, cls_pred))
+    return (kept, logits) if return_logits else kept

@@ -505,3 +505,77 @@ def test_evaluate_and_prediction_dict(dev, tmp_path):
             assert name == ["CAA", "Cored"][int(w[6])]
             n += 1
     assert n > 10
+
+
+# ------------------------------------------------------------------ consensus CAA filter
+def _caa_inputs():
+    from oracle.make_golden_caa import BOXES, NORM, caa_tile, seeded_caa_state
+    tile, state = caa_tile(11), seeded_caa_state(5)
+    xs = []
+    for box in BOXES:
+        xl, xr, yt, yb = R.get256img_box_faithful(box)
+        xs.append(R.caa_normalise(tile[yt:yb, xl:xr], NORM["mean"], NORM["std"]))
+    return tile, state, torch.stack(xs), NORM
+
+
+@pytest.mark.parametrize("precision,tol", [("bf16", 3e-2), ("fp32", 1e-4)])
+def test_caa_filter_network_vs_reference_golden(precision, tol, dev, golden):
+    """caa.Net on the engine (tcgen05 convolutions with the ReLU epilogue, 2x2 max-pool, AY_LINEAR output layer) against
+    the logits the UNMODIFIED core.Net produced for the same seeded weights and crops (tests/golden/caa_ref.npz).
+    Tolerance relative to the largest logit: 1e-4 in the fp32 mode (north_star's fp32 bar); 3e-2 in bf16 - the
+    network's inputs are normalised floats in about [-6, 2.5], which the 16-bit path rounds to 8 mantissa bits at layer 0
+    (the detector's uint8 pixels are exact there), on top of six layers of bf16 storage."""
+    from amyloid_yolo_paper_b200 import caa
+    _, state, x, _ = _caa_inputs()
+    want = golden("caa_ref.npz")["logits"]
+    net = caa.Net(precision=precision)
+    net.load_state_dict(state)
+    got = net(x.to(dev)).cpu().numpy()
+    assert got.shape == want.shape
+    err = np.abs(got - want).max() / np.abs(want).max()
+    print("caa.Net %s: logits rel err %.3e (bar %.0e)" % (precision, err, tol))
+    assert err <= tol
+    # a second call with one crop (engine reuse, batch 1) returns the same row
+    one = net(x[3:4].to(dev)).cpu().numpy()
+    assert np.array_equal(one[0], got[3])
+    # ReLU really is ReLU: the layer-0 output of the engine has no negative value and matches relu(bn(conv))
+    y0 = net.engine(dev).layer_output(0, 2).cpu()
+    assert float(y0.min()) >= 0.0 and float((y0 == 0).float().mean()) > 0.05
+
+
+def test_caa_filter_end_to_end_vs_oracle(dev):
+    """filterDetectionsByCAAModel on an in-memory tile against the oracle's restatement of core.py:425-452 (float64
+    network): same set-ordered rows, the same keep / drop decision for every box whose CAA logit is not within 0.05 of
+    the threshold, "Cored" boxes always kept, duplicates collapsed."""
+    from amyloid_yolo_paper_b200 import caa
+    from oracle.make_golden_caa import BOXES, CLASSES
+    tile, state, _, norm = _caa_inputs()
+    rng = np.random.default_rng(3)
+    dets = []
+    for i, (x, y, w, h) in enumerate(BOXES):
+        for cls in (0.0, 1.0):
+            dets.append([float(x), float(y), float(x + w), float(y + h), float(rng.uniform(0.8, 1)),
+                         float(rng.uniform(0.5, 1)), cls])
+    dets.append(list(dets[5]))                                              # an exact duplicate row
+    dets = torch.tensor(dets, dtype=torch.float32)
+    net = caa.Net()                                                         # fp32 mode
+    net.load_state_dict(state)
+    got, scores = caa.filterDetectionsByCAAModel(torch.from_numpy(tile), dets, CLASSES, model=net, norm=norm,
+                                                 device=dev, return_scores=True)
+    want, logits = R.caa_filter_faithful(tile, dets.numpy(), CLASSES, state, norm["mean"], norm["std"], return_logits=True)
+    order = list(set(tuple(r) for r in dets.tolist()))
+    assert len(order) == len(dets) - 1 == len(scores) == len(logits)
+    sure = {row for row, z in zip(order, logits) if abs(z) > 0.05}
+    got_rows = [tuple(r) for r in got.tolist()]
+    assert [r for r in got_rows if r in sure] == [r for r in want if r in sure]          # same rows, same (set) order
+    assert all(r in got_rows for r in order if CLASSES[int(r[6])] != "CAA")
+    dropped = len(order) - len(got_rows)
+    z = np.asarray(logits)
+    s = np.asarray(scores)[:, 2]
+    assert np.abs(s - 1 / (1 + np.exp(-z))).max() < 1e-4
+    print("CAA filter: %d distinct rows, %d kept by the oracle, %d by the engine, CAA logits %.2f .. %.2f"
+          % (len(order), len(want), len(got_rows), z.min(), z.max()))
+    assert 3 <= dropped <= len(order) // 2
+    # nothing to filter
+    empty = caa.filterDetectionsByCAAModel(torch.from_numpy(tile), torch.zeros((0, 7)), CLASSES, model=net, norm=norm, device=dev)
+    assert empty.numel() == 0

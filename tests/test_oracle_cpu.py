@@ -208,3 +208,45 @@ def test_evaluation_statistics_vs_reference_golden(golden):
             assert len(m) == int(g["st_n_%d_%d" % (s, int(thr * 100))][0])
             for i, (tp, sc, lb) in enumerate(m):
                 assert np.array_equal(tp, g["st_tp_%d_%d_%d" % (s, int(thr * 100), i)])
+
+
+def test_caa_filter_pieces_vs_reference_golden(golden):
+    """SURVEY §8f N2.  Against outputs of the unmodified reference (oracle/make_golden_caa.py: core.get256Img, core.Net,
+    torchvision's ToTensor + Normalize): the oracle's crop windows, its normalisation and its float64 restatement of the
+    network; and the product's host-side crop rule (caa.crop_window) against the oracle's branch-for-branch restatement
+    on every centre position near the comparisons."""
+    from amyloid_yolo_paper_b200 import caa
+    from oracle.make_golden_caa import BOXES, NORM, caa_tile, seeded_caa_state
+    g = golden("caa_ref.npz")
+    tile, state = caa_tile(11), seeded_caa_state(5)
+    xs = []
+    for box, win, ns in zip(BOXES, g["windows"], g["norm_sum"]):
+        assert R.get256img_box_faithful(box) == tuple(int(v) for v in win), box
+        assert caa.crop_window(box) == tuple(int(v) for v in win), box
+        xl, xr, yt, yb = win
+        assert np.array_equal(caa.get256Img(tile, box), tile[yt:yb, xl:xr])
+        x = R.caa_normalise(tile[yt:yb, xl:xr], NORM["mean"], NORM["std"])
+        assert float(x.double().sum()) == ns[0] and float(x[:, 17, 201].double().sum()) == ns[1]     # same fp32 bits
+        xs.append(x)
+    with torch.no_grad():
+        logits = R.caa_net_forward(state, torch.stack(xs)).numpy()
+    assert np.abs(logits - g["logits"]).max() <= 1e-4 * np.abs(g["logits"]).max()                     # fp32 reference vs float64
+    # the product's per-axis rule == the reference's nine branches, for every centre within 3 pixels of a comparison
+    edge = [c for c in range(0, 1537) if min(abs(c - 128), abs(c - 1408), c, 1536 - c) <= 3] + [700]
+    for cx in edge:
+        for cy in edge:
+            box = (cx - 10, cy - 7, 20, 14)
+            assert caa.crop_window(box) == R.get256img_box_faithful(box), box
+    # parameter names of the product's Net are the reference's (the pickled model's state_dict loads)
+    net = caa.Net()
+    assert set(net.state_dict()) == set(state)
+    net.load_state_dict(state)
+    w, b = caa.fold_stage(state, 2)
+    y_ref = torch.nn.functional.batch_norm(
+        torch.nn.functional.conv2d(torch.ones(1, 32, 5, 5, dtype=torch.float64), state["features.8.weight"].double(),
+                                   state["features.8.bias"].double(), padding=1),
+        state["features.9.running_mean"].double(), state["features.9.running_var"].double(),
+        state["features.9.weight"].double(), state["features.9.bias"].double(), False, 0.0, 1e-5)
+    y_fold = torch.nn.functional.conv2d(torch.ones(1, 32, 5, 5, dtype=torch.float64), torch.from_numpy(w).double(),
+                                        torch.from_numpy(b).double(), padding=1)
+    assert float((y_ref - y_fold).abs().max()) < 1e-5
