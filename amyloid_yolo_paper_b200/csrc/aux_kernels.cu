@@ -9,6 +9,7 @@
 //   ref_conv        CUDA-core direct convolution, test cross-check of the tcgen05 kernel
 //   decode          stand-alone YOLO decode (models.py:137-169) used with ref_conv
 //   linear          fully connected output layer of the CAA filter network (core.py:161-205)
+//   wsi_gather      slide in HBM -> the 416^2 detector inputs of its 1536^2 tiles (crop.py:13-25 + the resize)
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -462,6 +463,45 @@ int launch_linear(const void* act, int elem_bytes, int is_fp16, int pitch, int l
                   const float* w, const float* bias, int O, float* out, cudaStream_t s) {
   if (batch < 1 || O < 1 || C < 1 || H < 1 || W < 1) { set_error("linear: bad shape"); return AY_EINVAL; }
   linear_kernel<<<dim3(O, batch), 128, 0, s>>>(act, elem_bytes, is_fp16, pitch, lo, hi, C, H, W, w, bias, O, out);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+// ---------------------------------------------------------------- slide -> detector input
+// The reference cuts a slide into 1536^2 JPEG tiles (crop.py:13-25, dzsave layout google: tile (row, col) starts at
+// (row*T, col*T), edge tiles padded with the white background) and later resizes every tile to 416^2 with nearest
+// sampling (utils/transforms.py:104-111).  With the slide resident in HBM both steps are one gather: output pixel
+// (y, x) of tile (row, col) is slide pixel (row*T + idx(y), col*T + idx(x)), idx(i) = min(floor(i * float(T)/float(S)), T-1)
+// (ATen's nearest index, as engine.cu nearest_table), `background` outside the slide.  Reads (S/T)^2 = 7 % of the slide.
+namespace {
+__global__ void __launch_bounds__(256)
+wsi_gather_kernel(const uint8_t* __restrict__ wsi, int height, int width, long long pitch, int T, int S, int row0, int col0,
+                  int n_rows, int n_cols, uint8_t* __restrict__ out, int background) {
+  const long long total = (long long)n_rows * n_cols * S * S;
+  const float scale = (float)T / (float)S;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(i % S), y = (int)((i / S) % S);
+    const int t = (int)(i / ((long long)S * S));
+    const int row = row0 + t / n_cols, col = col0 + t % n_cols;
+    int sy = (int)floorf(__fmul_rn((float)y, scale)), sx = (int)floorf(__fmul_rn((float)x, scale));
+    sy = sy < T - 1 ? sy : T - 1;
+    sx = sx < T - 1 ? sx : T - 1;
+    const long long gy = (long long)row * T + sy, gx = (long long)col * T + sx;
+    uint8_t r = (uint8_t)background, g = r, b = r;
+    if (gy < height && gx < width) {
+      const uint8_t* src = wsi + gy * pitch + gx * 3;
+      r = __ldg(src); g = __ldg(src + 1); b = __ldg(src + 2);
+    }
+    uint8_t* o = out + i * 3;
+    o[0] = r; o[1] = g; o[2] = b;
+  }
+}
+}  // namespace
+
+int launch_wsi_gather(const uint8_t* wsi, int height, int width, long long pitch, int T, int S, int row0, int col0, int n_rows,
+                      int n_cols, uint8_t* out, int background, cudaStream_t s) {
+  const long long total = (long long)n_rows * n_cols * S * S;
+  wsi_gather_kernel<<<grid_for(total), 256, 0, s>>>(wsi, height, width, pitch, T, S, row0, col0, n_rows, n_cols, out, background);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

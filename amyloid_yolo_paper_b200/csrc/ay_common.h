@@ -176,6 +176,8 @@ struct DecodeParams {
   int lo, hi;            // zero pixels before / after each row and column of `raw`'s padded grid
 };
 int launch_decode(const DecodeParams& p, cudaStream_t s);
+int launch_wsi_gather(const uint8_t* wsi, int height, int width, long long pitch, int T, int S, int row0, int col0, int n_rows,
+                      int n_cols, uint8_t* out, int background, cudaStream_t s);
 // fully connected output layer over a zero-haloed NHWC activation (16-bit: elem_bytes 2, fp32: 4); w [O][H*W*C] in
 // (y, x, c) order, out [batch][O]
 int launch_linear(const void* act, int elem_bytes, int is_fp16, int pitch, int lo, int hi, int batch, int C, int H, int W,

@@ -1470,6 +1470,20 @@ extern "C" int ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* c
                                   static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int ay_wsi_gather(ay_ctx* ctx, const uint8_t* wsi, int height, int width, long long pitch_bytes, int tile_size,
+                             int out_size, int row0, int col0, int n_rows, int n_cols, uint8_t* out, int background,
+                             void* stream) {
+  AY_ENTER(ctx);
+  if (!wsi || !out || height < 1 || width < 1 || pitch_bytes < 3LL * width || tile_size < 1 || out_size < 1 ||
+      out_size > tile_size || row0 < 0 || col0 < 0 || n_rows < 1 || n_cols < 1 || background < 0 || background > 255) {
+    set_error("ay_wsi_gather: bad arguments (slide %dx%d pitch %lld, tile %d -> %d, tiles %d..+%d x %d..+%d)", height, width,
+              pitch_bytes, tile_size, out_size, row0, n_rows, col0, n_cols);
+    return AY_EINVAL;
+  }
+  return ay::launch_wsi_gather(wsi, height, width, pitch_bytes, tile_size, out_size, row0, col0, n_rows, n_cols, out, background,
+                               static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int ay_bbox_iou(ay_ctx* ctx, const float* box1, int n1, const float* box2, int n2, float* out_iou,
                            void* stream) {
   AY_ENTER(ctx);

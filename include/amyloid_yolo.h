@@ -135,6 +135,15 @@ int  ay_nms_timed(ay_ctx* ctx, float* pred, int batch, int n_rows, int n_classes
 int  ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* counts, int batch, int cap,
                       int current_dim, int orig_h, int orig_w, int merge,
                       float* out_rows, int32_t* out_counts, void* stream);
+/* crop.py:13-25 (dzsave, layout google, tile_size 1536, depth one) followed by the nearest Resize of
+ * utils/transforms.py:104-111, for a slide (or slide region) already in device memory: wsi is [height, width, 3] uint8
+ * with rows pitch_bytes apart; tile (row, col) covers slide pixels [row*tile_size, +tile_size) x [col*tile_size, ...),
+ * padded with `background` (dzsave pads edge tiles white, 255) where it leaves the slide.  Writes the out_size^2
+ * pixels the resize samples from each of the n_rows x n_cols tiles starting at (row0, col0), row-major, as
+ * out [n_rows*n_cols, out_size, out_size, 3] uint8 - the AY_IN_U8_HWC input of ay_forward.  The JPEG (Q=90) round trip of
+ * the reference's tile files is not reproduced.                                        */
+int  ay_wsi_gather(ay_ctx* ctx, const uint8_t* wsi, int height, int width, long long pitch_bytes, int tile_size,
+                   int out_size, int row0, int col0, int n_rows, int n_cols, uint8_t* out, int background, void* stream);
 /* bbox_iou (utils/utils.py:202-232, x1y1x2y2=True): iou[i] of box1[i or 0] vs box2[i]. */
 int  ay_bbox_iou(ay_ctx* ctx, const float* box1, int n1, const float* box2, int n2,
                  float* out_iou, void* stream);

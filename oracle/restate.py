@@ -795,3 +795,44 @@ def caa_filter_faithful(img_rgb_u8, detections, classes, state, mean, std, dtype
             continue
         kept.append((x1, y1, x2, y2, conf, cls_conf, cls_pred))
     return (kept, logits) if return_logits else kept
+
+
+# --------------------------------------------------------------------------
+# slide tiling: crop.py:13-25 (dzsave layout google, tile_size 1536, depth one) + the detector's resize.
+# PARITY UNPINNED: pyvips / openslide are absent, the reference's tiler cannot be run here; this restates the published
+# dzsave layout (tile (row, col) at (row*T, col*T), edge tiles padded white) without the JPEG round trip.
+# --------------------------------------------------------------------------
+def wsi_tiles_faithful(slide, tile_size=1536, background=255):
+    """-> dict {(row, col): [T,T,3] uint8} in the reference's two steps: pad, cut."""
+    h, w = slide.shape[:2]
+    rows, cols = -(-h // tile_size), -(-w // tile_size)
+    canvas = np.full((rows * tile_size, cols * tile_size, 3), background, dtype=np.uint8)
+    canvas[:h, :w] = slide
+    return {(r, c): canvas[r * tile_size:(r + 1) * tile_size, c * tile_size:(c + 1) * tile_size]
+            for r in range(rows) for c in range(cols)}
+
+
+def wsi_detector_inputs_faithful(slide, img_size=416, tile_size=1536):
+    """Each padded tile through the nearest resize (utils/transforms.py:104-111) -> {(row, col): [S,S,3] uint8}."""
+    idx = nearest_src_index(img_size, tile_size)
+    return {k: t[idx][:, idx] for k, t in wsi_tiles_faithful(slide, tile_size).items()}
+
+
+def divide_and_conquer_faithful(height, width, multiple=1536 * 16):
+    """crop.py:63-92 with the branch structure of the reference: full-size crop unless the chunk touches the bottom
+    and/or right edge, where the except-branches shrink it.  -> [(indice, left, top, w, h)]."""
+    out, indice = [], 0
+    tops, lefts = list(range(0, height, multiple)), list(range(0, width, multiple))
+    for top in tops:
+        for left in lefts:
+            indice += 1
+            if left + multiple <= width and top + multiple <= height:          # vips crop succeeds
+                out.append((indice, left, top, multiple, multiple))
+            elif top == tops[-1] and left == lefts[-1]:
+                out.append((indice, left, top, width - left, height - top))
+            else:
+                if top == tops[-1]:
+                    out.append((indice, left, top, multiple, height - top))
+                if left == lefts[-1]:
+                    out.append((indice, left, top, width - left, multiple))
+    return out

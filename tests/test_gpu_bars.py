@@ -579,3 +579,45 @@ def test_caa_filter_end_to_end_vs_oracle(dev):
     # nothing to filter
     empty = caa.filterDetectionsByCAAModel(torch.from_numpy(tile), torch.zeros((0, 7)), CLASSES, model=net, norm=norm, device=dev)
     assert empty.numel() == 0
+
+
+# ------------------------------------------------------------------ slide tiling fused with the resize
+def test_slide_gather_and_detect_slide(dev):
+    """ay_wsi_gather on a ragged slide (not a multiple of 1536 either way) against the oracle's pad -> cut -> nearest
+    resize, bit for bit, for whole grids and sub-blocks, and on a strided view of a larger slide; crop.detect_slide
+    returns for every tile exactly what TileDetector.detect returns for the explicitly cut and padded 1536^2 tile."""
+    from amyloid_yolo_paper_b200 import crop, synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    rng = np.random.default_rng(5)
+    H, W = 2 * 1536 + 700, 3 * 1536 + 11
+    slide = np.ascontiguousarray(synth.synthetic_tiles(12, size=1536, seed=3).reshape(3, 4, 1536, 1536, 3)
+                                 .transpose(0, 2, 1, 3, 4).reshape(3 * 1536, 4 * 1536, 3)[:H, :W])
+    slide[::7, ::5] = rng.integers(0, 256, slide[::7, ::5].shape, dtype=np.uint8)
+    want = R.wsi_detector_inputs_faithful(slide, 416, 1536)
+    assert sorted(want) == [(r, c) for r in range(3) for c in range(4)]
+    big = torch.zeros((H + 9, W + 5, 3), dtype=torch.uint8, device=dev)
+    big[:H, :W] = torch.from_numpy(slide).to(dev)
+    for s in (torch.from_numpy(slide).to(dev), big[:H, :W]):                 # packed, then a strided view
+        got = crop.detector_inputs(s, 0, 0, 3, 4).cpu().numpy()
+        for r in range(3):
+            for c in range(4):
+                assert np.array_equal(got[r * 4 + c], want[(r, c)]), (r, c)
+        sub = crop.detector_inputs(s, 1, 2, 2, 2).cpu().numpy()
+        assert np.array_equal(sub[3], want[(2, 3)]) and np.array_equal(sub[0], want[(1, 2)])
+    assert (want[(2, 3)][-1, -1] == 255).all()                                # the white padding is sampled
+    small = R.wsi_detector_inputs_faithful(slide[:300, :450], 64, 128)        # another tile / output size
+    got = crop.detector_inputs(torch.from_numpy(np.ascontiguousarray(slide[:300, :450])).to(dev), 0, 0, 3, 4, 64, 128).cpu().numpy()
+    assert all(np.array_equal(got[r * 4 + c], small[(r, c)]) for r in range(3) for c in range(4))
+    # whole-slide detection == per-tile detection of the explicitly padded tiles
+    m, _ = _model(ensure_cfg("yolov3-custom"), seed=1, conf_bias=-2.5, wh_gain=0.15)
+    det = TileDetector(m, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=5, cap=512, device=dev)
+    tiles = R.wsi_tiles_faithful(slide)
+    n = 0
+    for r, c, d in crop.detect_slide(det, torch.from_numpy(slide).to(dev)):
+        ref = det.detect(torch.from_numpy(np.ascontiguousarray(tiles[(r, c)]))[None].to(dev))[0]
+        assert (d is None) == (ref is None), (r, c)
+        if d is not None:
+            assert torch.equal(d.view(torch.int32), ref.view(torch.int32)), (r, c)
+            n += len(d)
+    assert n > 0

@@ -229,3 +229,32 @@ def test_loader_gather_equals_reference_transform_chain(tmp_path):
     flat = [t for g in got for t in g[1]]
     for a, t in zip(imgs, flat):
         assert np.array_equal(t.numpy(), gather_resized(a, 32))
+
+
+def test_slide_tiling_host_logic(tmp_path):
+    """grid / names / divide-and-conquer chunks against the oracle's branch-for-branch
+    restatement, and save_and_tile's directory layout with white-padded edge tiles.  (Parity with pyvips itself is
+    unpinned: it is not installed.)"""
+    from PIL import Image
+    from amyloid_yolo_paper_b200 import crop
+    from oracle import restate as R
+    for h, w in [(1536, 1536), (1537, 1535), (24576, 24576), (24577, 49152), (30000, 50000), (100, 73729), (73728, 24575)]:
+        assert crop.divide_and_conquer_chunks(h, w) == R.divide_and_conquer_faithful(h, w), (h, w)
+        rows, cols = crop.tile_grid(h, w)
+        assert (rows - 1) * 1536 < h <= rows * 1536 and (cols - 1) * 1536 < w <= cols * 1536
+    assert crop.tile_name(3, 7) == "0/3/7.jpg" and crop.chunk_basename(2, "s.svs") == "2_s.svs"
+    rng = np.random.default_rng(0)
+    slide = rng.integers(0, 200, (300, 450, 3), dtype=np.uint8)
+    want = R.wsi_tiles_faithful(slide, 128)
+    assert sorted(want) == [(r, c) for r in range(3) for c in range(4)]
+    for (r, c), t in want.items():
+        assert np.array_equal(crop.padded_tile(slide, r, c, 128), t)
+    assert (want[(2, 3)][44:, :] == 255).all() and (want[(2, 3)][:, 66:] == 255).all()
+    flat = np.full((300, 450, 3), 90, dtype=np.uint8)                       # flat colour survives JPEG: layout check
+    files = crop.save_and_tile(flat, str(tmp_path), "slideA.svs", tile_size=128)
+    assert len(files) == 12 and os.path.isfile(os.path.join(str(tmp_path), "slideA", "0", "2", "3.jpg"))
+    edge = np.asarray(Image.open(os.path.join(str(tmp_path), "slideA", "0", "2", "3.jpg")))
+    assert edge.shape == (128, 128, 3) and abs(int(edge[10, 10, 0]) - 90) <= 2 and int(edge[100, 100, 0]) >= 250
+    assert crop.halve(np.full((5, 7, 3), 11, np.uint8)).shape == (2, 3, 3)
+    with pytest.raises(ValueError):
+        crop.detector_inputs(torch.zeros((10, 10, 3), dtype=torch.uint8), 0, 0, 1, 1)      # host tensor: no CPU path
