@@ -12,6 +12,9 @@ over NCCL (NVLink/NVSwitch) on the GPU box, gloo in the CPU tests.  No activatio
 weight traffic; each rank holds a full weight replica.
 """
 import itertools
+import os
+import sys
+import time
 
 import torch
 import torch.distributed as dist
@@ -75,6 +78,8 @@ def allgather_detections(rows, counts, n_tiles, group=None):
     all_rows = torch.empty((world * per_rank, k, 7), dtype=torch.float32, device=dev)
     dist.all_gather_into_tensor(all_counts, send_counts, group=group)
     dist.all_gather_into_tensor(all_rows, send_rows, group=group)
+    if per_rank * world == int(n_tiles):                     # even shards: nothing to drop
+        return all_rows, all_counts
     # drop the padding tiles of the ranks that own one tile fewer
     sel = []
     for r in range(world):
@@ -82,6 +87,38 @@ def allgather_detections(rows, counts, n_tiles, group=None):
         sel.extend(range(r * per_rank, r * per_rank + (rhi - rlo)))
     sel = torch.tensor(sel, dtype=torch.long, device=dev)
     return all_rows.index_select(0, sel), all_counts.index_select(0, sel)
+
+
+def warm_gather(n_tiles, kmax, device, group=None):
+    """One exchange of the shape a sweep over ``n_tiles`` tiles with lists of up to ``kmax`` rows will make, on zeros.
+    NCCL sets up the connections of each protocol the first time a message size selects it, and the caching allocator
+    has to get the gather buffers from the driver once: tens of milliseconds at 8 ranks, which a production sweep of
+    10^5 tiles never notices but a 10-step measurement does.  Call it once before timing anything."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 2:
+        return
+    lo, hi = shard_range(n_tiles, dist.get_rank(group), dist.get_world_size(group))
+    rows = torch.zeros((hi - lo, max(int(kmax), 1), 7), dtype=torch.float32, device=device)
+    counts = torch.zeros((hi - lo,), dtype=torch.int32, device=device)
+    allgather_detections(rows, counts, n_tiles, group)
+    if torch.device(device).type == "cuda":
+        torch.cuda.synchronize(device)
+
+
+def _phase_timer(device):
+    """AY_SWEEP_TIMING=1: wall-clock of the sweep's phases on stderr (synchronises at every phase boundary)."""
+    if not os.environ.get("AY_SWEEP_TIMING"):
+        return lambda name: None
+    state = {"t": time.perf_counter()}
+
+    def mark(name):
+        if torch.device(device).type == "cuda":
+            torch.cuda.synchronize(device)
+        now = time.perf_counter()
+        rank = dist.get_rank() if dist.is_initialized() else 0
+        if rank == 0:
+            sys.stderr.write("[sweep] %-10s %8.2f ms\n" % (name, 1e3 * (now - state["t"])))
+        state["t"] = now
+    return mark
 
 
 def sweep(detector, tile_source, n_tiles, batch, group=None, gather=True):
@@ -97,6 +134,7 @@ def sweep(detector, tile_source, n_tiles, batch, group=None, gather=True):
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     lo, hi = shard_range(n_tiles, rank, world)
     nccl = dist.is_initialized() and dist.get_backend(group) == "nccl"
+    mark = _phase_timer(detector.device)
     batches = (tile_source(b0, min(hi, b0 + batch)) for b0 in range(lo, hi, batch))
     first = next(batches, None)
     if first is not None and first.is_cuda:
@@ -111,6 +149,7 @@ def sweep(detector, tile_source, n_tiles, batch, group=None, gather=True):
             counts[at:at + n].copy_(c)
             at += n
         detector.check()                                   # capacity overflows / device faults surface here
+        mark("compute")
         kmax = max(int(counts.max().item()), 1) if hi > lo else 1
         rows = rows[:, :kmax].contiguous()
         # rows beyond a tile's count hold whatever the previous occupant of the slot left: zero them so that the
@@ -126,6 +165,9 @@ def sweep(detector, tile_source, n_tiles, batch, group=None, gather=True):
             for outs in detector.detect_stream(itertools.chain([first], batches)):
                 per_tile.extend(outs)
         rows, counts = pack_detections(per_tile, device=detector.device if nccl else None)
+    mark("pack")
     if gather and world > 1:
-        return allgather_detections(rows, counts, n_tiles, group)
+        out = allgather_detections(rows, counts, n_tiles, group)
+        mark("gather")
+        return out
     return rows, counts

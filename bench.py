@@ -96,7 +96,7 @@ def profiled_traffic(batch):
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    FIELDS = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
 
@@ -104,13 +104,23 @@ class ClockSampler:
         self.index = index
         self.proc = None
         self.path = None
+        self.spans = []          # wall-clock [begin, end] of the timed regions: only samples inside them are reported
+        self._t0 = None
+
+    def begin(self):
+        self._t0 = time.time()
+
+    def end(self):
+        if self._t0 is not None:
+            self.spans.append((self._t0, time.time()))
+            self._t0 = None
 
     def start(self):
         try:
             fd, self.path = tempfile.mkstemp(prefix="clocks_", suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -124,26 +134,35 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, names = [], ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        seen = set()
+        import datetime
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []                                             # (epoch seconds or None, sm MHz, set of active reasons)
         for line in open(self.path):
             parts = [v.strip() for v in line.split(",")]
-            if len(parts) < 7:
+            if len(parts) < 8:
                 continue
             try:
-                sm.append(float(parts[0]))
-                out["sm_max_mhz"] = float(parts[1])
+                mhz = float(parts[1])
+                out["sm_max_mhz"] = float(parts[2])
             except ValueError:
                 continue
-            for name, v in zip(names, parts[3:7]):
-                if v.lower().startswith("active"):
-                    seen.add(name)
+            try:
+                ts = datetime.datetime.strptime(parts[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+            except ValueError:
+                ts = None
+            rows.append((ts, mhz, {n for n, v in zip(names, parts[4:8]) if v.lower().startswith("active")}))
         os.unlink(self.path)
+        # a sample counts when it was taken inside a timed region (a query takes a few ms: 20 ms of slack at the start)
+        inside = [r for r in rows if r[0] is not None and any(a + 0.02 <= r[0] <= b for a, b in self.spans)]
+        scope = "timed regions"
+        if not inside:
+            inside, scope = rows, "whole run (no sample fell inside a timed region)"
+        sm = sorted(r[1] for r in inside)
         if sm:
-            sm.sort()
             out["sm_mhz"] = sm[len(sm) // 2]
         out["samples"] = len(sm)
-        out["reasons"] = sorted(seen)
+        out["reasons"] = sorted(set().union(*[r[2] for r in inside])) if inside else []
+        out["scope"] = scope
         return out
 
 
@@ -368,11 +387,13 @@ def nms_arm(args):
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)
+    clocks.begin()
     e0.record(stream)
     for _ in range(K):
         step()
     e1.record(stream)
     torch.cuda.synchronize(dev)
+    clocks.end()
     _lib.check(lib.ay_check(ctx, st))
     ms = e0.elapsed_time(e1)
     kept = int(counts.sum().item())
@@ -412,7 +433,8 @@ def nms_arm(args):
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(args),
             "gpu_launches": 4 * K,
-            "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"], "samples": clk["samples"]},
+            "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"], "samples": clk["samples"],
+                       "scope": clk.get("scope")},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s", "frac": achieved / peaks["hbm"],
                          "traffic": None, "kernel": "nms_mask_kernel (IoU > thres bit matrix, 64x64 blocks)",
                          "ms": parts[1], "algorithmic_bytes_per_launch": algo, "peak_source": peaks["source"] + " (hbm_gbs)",
@@ -486,13 +508,18 @@ def main():
             r, c = det.run_device(tiles, orig)
         return r, c
 
-    run_sweep(W)
+    warm_rows, _ = run_sweep(W)
     det.check()
+    if world > 1 and B >= 8 and not os.environ.get("AY_NO_WARM_GATHER"):
+        # the K-step sweep's exchange is larger than the W-step one: set up its NCCL protocol and buffers outside the
+        # timed region (sweep.warm_gather: zeros of the same shape; no detection work is moved out of the timing)
+        sweep.warm_gather(world * B * K, warm_rows.shape[1], dev)
     launches_per_step = det.launches_per_batch
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clocks = ClockSampler(local)
-    barrier()
-    clocks.start()
+    clocks.start()               # (before the barrier: spawning the sampler takes tens of ms, different on every rank -
+    barrier()                    #  ranks that entered the timed region early would wait for the late one in the gather)
+    clocks.begin()
     if B >= 8:
         e0.record(stream)
         rows, counts = run_sweep(K)
@@ -509,11 +536,13 @@ def main():
             b.record(stream)
         barrier()
         ms = sum(a.elapsed_time(b) for a, b in evs)
+    clocks.end()
     det.check()
     n_det = int(counts.clamp(min=0).sum().item()) // (world * K if B >= 8 else 1)
 
     # ---- conv stack alone (roofline numerator): events around ay_forward, same inputs, same stream
     fwd_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    clocks.begin()
     for a, b in fwd_ev:
         if flush is not None:
             flush.zero_()
@@ -522,6 +551,7 @@ def main():
                                       ctypes.c_void_p(det.decoded.data_ptr()), ctypes.c_void_p(stream.cuda_stream)))
         b.record(stream)
     torch.cuda.synchronize(dev)
+    clocks.end()
     fwd_mean = sum(a.elapsed_time(b) for a, b in fwd_ev) / K
     fwd_launches = det.engine.launch_count()
 
@@ -569,6 +599,7 @@ def main():
             for _ in range(2):
                 det.detect(batch_host, orig)
             barrier()
+            clocks.begin()
             t0 = time.perf_counter()
             n_out = 0
             per_tile = []
@@ -580,6 +611,7 @@ def main():
                 sweep.allgather_detections(r_, c_, world * B * K)
             barrier()
             dt = time.perf_counter() - t0
+            clocks.end()
             assert n_out == K * B
             return dt, det.d2h_bytes // K
 
@@ -635,10 +667,15 @@ def main():
             e2e["import_swap_api"] = {"value": K / times[-1], "ms_per_tile": 1000.0 * times[-1] / K,
                                       "call": "Darknet.forward (CPU tensor in, decoded CPU tensor out) + non_max_suppression + "
                                               "rescale_boxes + mergeDetections"}
-    clk = clocks.stop()          # sampled over all timed regions: every one of them is under load
+    clk = clocks.stop()          # samples taken inside the timed regions (value, conv stack, e2e streams)
 
+    per_rank = None
     if world > 1:
         t = torch.tensor([ms, fwd_mean], dtype=torch.float64, device=dev)
+        every = torch.empty((world, 2), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(every, t)
+        per_rank = {"ms_per_step": [round(float(v) / K, 3) for v in every[:, 0].tolist()],
+                    "conv_stack_ms": [round(float(v), 3) for v in every[:, 1].tolist()]}
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, fwd_mean = (float(v) for v in t.tolist())
 
@@ -654,7 +691,7 @@ def main():
             "data": "synthetic", "config": workload_config(args),
             "gpu_launches": int(launches_per_step * K),
             "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
-                       "samples": clk["samples"]},
+                       "samples": clk["samples"], "scope": clk.get("scope")},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16"], "unit": "TFLOP/s",
                          "frac": achieved / peaks["bf16"], "traffic": traffic, "traffic_unit": "DRAM bytes per ay_forward",
                          "traffic_source": traffic_src,
@@ -674,6 +711,8 @@ def main():
             line["e2e"] = e2e
         if gather_verified is not None:
             line["gather_verified"] = gather_verified
+        if per_rank is not None:
+            line["per_rank"] = per_rank          # max over ranks is what `value` and the roofline use
         emit(args, line)
     if world > 1:
         dist.barrier()
