@@ -730,13 +730,20 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               f[2 * q + 0] = add2(make_float2(__uint_as_float(v[4 * q + 0]), __uint_as_float(v[4 * q + 1])), make_float2(bb.x, bb.y));
               f[2 * q + 1] = add2(make_float2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])), make_float2(bb.z, bb.w));
             }
-            if (p.leaky) {
-              const float slope = act_slope(p.leaky);            // 0.1 LeakyReLU, 0 ReLU
+            // (two branches with immediate operands: a slope held in registers across this block made ptxas spill loop
+            // state of the epilogue - 28 bytes instead of 4 - and cost layers 0-3 10-20 %)
+            if (p.leaky == 1) {
 #pragma unroll
-              for (int e = 0; e < 16; ++e) {                     // max(x, s*x) == (x > 0 ? x : s*x) for every x, 0 <= s < 1
-                const float2 s = mul2(f[e], make_float2(slope, slope));
+              for (int e = 0; e < 16; ++e) {                     // max(x, 0.1x) == (x > 0 ? x : 0.1x) for every x
+                const float2 s = mul2(f[e], make_float2(0.1f, 0.1f));
                 f[e].x = fmaxf(f[e].x, s.x);
                 f[e].y = fmaxf(f[e].y, s.y);
+              }
+            } else if (p.leaky == 2) {                           // ReLU (the CAA filter network, core.py:165-198)
+#pragma unroll
+              for (int e = 0; e < 16; ++e) {
+                f[e].x = fmaxf(f[e].x, 0.f);
+                f[e].y = fmaxf(f[e].y, 0.f);
               }
             }
             uint32_t o[16];
