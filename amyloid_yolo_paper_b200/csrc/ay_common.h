@@ -106,7 +106,6 @@ struct ConvGemmParams {
   int plane_packed;      // 32-channel producer: the column-parity pair shares one 64-channel row of a ROW-parity plane
   // fused YOLO decode (head convolutions)
   int head;
-  int tma_store;         // row-mode layer: results leave through shared-memory boxes and TMA stores (head_stage_bytes = 4096 per warp)
   int head_fast;         // 3 anchors x 7 columns in one chunk: compile-time channel roles, MUFU exp / reciprocal
   int head_stage_bytes;  // per epilogue warp: n_anchors * 32 * dec_cols floats when the head fits one 32-column chunk, else 0
   float* dec_out;        // [B, dec_rows_total, dec_cols]
@@ -126,8 +125,8 @@ struct ConvGemmParams {
 constexpr int kProfStampBase = 16;
 constexpr int kProfStampCtas = 160;                       // >= CTAs per launch (148)
 constexpr int kProfWords = kProfStampBase + 4 * kProfStampCtas;
-int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const ConvGemmParams& p, int G,
-                     int is_fp16, int num_sms, cudaStream_t stream);   // is_fp16: 0 bf16, 1 fp16, 2 tf32 (p.tf32 set)
+int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p, int G, int is_fp16,
+                     int num_sms, cudaStream_t stream);   // is_fp16: 0 bf16, 1 fp16, 2 tf32 (p.tf32 set)
 int conv_gemm_stage_bytes(int BN, int G, int a_rows, int resident);
 void conv_gemm_pick_smem(int BN, int G, int a_rows, int resident_bytes, int units_per_stage, int extra_bytes, int* stages, int* nbuf);
 #ifndef AY_EPI_PARTS

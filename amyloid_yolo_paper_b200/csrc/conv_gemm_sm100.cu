@@ -219,21 +219,6 @@ constexpr int kBiasFloats = 1024;
 constexpr int kBK = 64;                 // channels per k-block: one 128-byte swizzle row
 constexpr uint32_t kRowBytes = 128;
 
-// TMA box store from shared memory (epilogue staging of row-mode layers) and its bulk-group bookkeeping
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
-               : "memory");
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-}
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
 // 256-bit global accesses (sm_100): a thread moves one whole 32-byte sector per instruction
 __device__ __forceinline__ void ldg256(const void* ptr, uint32_t* v) {
   asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -277,7 +262,7 @@ __device__ __forceinline__ void append_candidates(const ConvGemmParams& p, bool 
 template <int G, bool FP16, bool SPLIT, bool TF32>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ ConvGemmParams p) {
+                 const __grid_constant__ ConvGemmParams p) {
   // shared memory: [S pipeline stages][epilogue staging][mbarriers][tmem slot][bias]
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_addr(smem_raw) + 1023u) & ~1023u;
@@ -334,7 +319,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
-    if (p.tma_store) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmOut)) : "memory");
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < S; ++s) {
@@ -582,7 +566,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       py = (int)(((unsigned long long)(unsigned)rem * p.div_wp_mul) >> p.div_wp_shift);
       px = rem - py * p.Wp;
     };
-    uint32_t tma_seq = 0;                                  // staged box stores issued by this warp (tma_store layers)
     for (; tile < total_tiles; tile += t_step) {
       const int n0 = ntile * p.BN;
       const bool in_range = m < p.P;
@@ -764,27 +747,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                   stg256(dst + 16, &o[8]);
                 }
               }
-            } else if (p.tma_store) {
-              // Row-mode layers with narrow tiles: the 32 rows x 64 bytes of this warp and chunk go through a shared-memory
-              // box (TMA SWIZZLE_64B layout: the 16-byte piece j of row r sits at piece j ^ ((r >> 1) & 3), which also makes
-              // the 128-bit shared stores of a quarter warp conflict-free) and leave as ONE TMA box store instead of 64 row
-              // accesses through L1TEX (ncu: l1tex 79 % busy, tensor pipe 25 %, in the layers this path is for).  Rows that
-              // must not change (halo pixels, rows past the batch) carry zeros: exactly what those rows hold.  Two boxes per
-              // warp alternate; a box is rewritten once the store before the previous one has finished READING it.
-              if (!t.store) {
-#pragma unroll
-                for (int e = 0; e < 16; ++e) o[e] = 0u;
-              }
-              const uint32_t box = staging_base + (uint32_t)ew * (uint32_t)p.head_stage_bytes + (uint32_t)(tma_seq & 1) * 2048u;
-              if (lane == 0) bulk_wait_read<1>();
-              __syncwarp();
-              const uint32_t rowb = box + (uint32_t)lane * 64u, sw = (uint32_t)(lane >> 1) & 3u;
-#pragma unroll
-              for (int j = 0; j < 4; ++j) sts128(rowb + ((uint32_t)j ^ sw) * 16u, o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
-              asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-              __syncwarp();
-              if (lane == 0 && !(p.dbg & 4)) tma_store_2d(&tmOut, box, n0 + ch, m - lane);
-              ++tma_seq;
             } else if (t.store && !(p.dbg & 4)) {
               if (p.plane_mode != 2) {
                 stg256(t.out + ch, &o[0]);
@@ -915,7 +877,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         m += tile_rows;
       }
     }
-    if (p.tma_store && lane == 0) bulk_wait_all();         // the staged boxes must have left before shared memory goes away
   }
 
   // both CTAs must stay resident until the pair's last MMA, commit and remote arrive have landed
@@ -960,8 +921,8 @@ static void magic_div(unsigned d, int nbits, unsigned* mul, int* shift) {
   *mul = (unsigned)(((1ull << *shift) + d - 1) / d);
 }
 
-int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const ConvGemmParams& p_in,
-                     int G, int is_fp16, int num_sms, cudaStream_t stream) {
+int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvGemmParams& p_in, int G, int is_fp16,
+                     int num_sms, cudaStream_t stream) {
   ConvGemmParams p = p_in;
   {
     // rows reach P rounded up to whole tiles (plus the row batch of the last one)
@@ -997,10 +958,6 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
   // by alternate warps of a TMEM lane quarter (SPLIT); wider tiles are shared chunk by chunk
   const int chunks = (p.BN * p.m_batch) >> 5;
   const bool split = chunks == 1 || (chunks <= kMaxChunksPerWarp && !p.head);
-  if (p.tma_store && (!split || p.head || p.up_mode || p.plane_mode != 0 || p.m_batch != 1 || p.tf32 || p.head_stage_bytes < 4096)) {
-    set_error("conv_gemm: staged TMA stores need a row-mode layer with tiles of at most %d chunks", kMaxChunksPerWarp);
-    return AY_EINVAL;
-  }
   if (split && (p.num_acc % kEpiParts) != 0) { set_error("conv_gemm: %d accumulators cannot be shared by tile", p.num_acc); return AY_EINVAL; }
   {
     const int t_step = (grid / 2) * (split ? kEpiParts : 1);
@@ -1024,7 +981,7 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
 #define AY_LAUNCH4(GG, FF, SS, TT)                                                                                            \
   do {                                                                                                                        \
     AY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<GG, FF, SS, TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
-    AY_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<GG, FF, SS, TT>, tmA, tmB, tmOut, p));                                  \
+    AY_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<GG, FF, SS, TT>, tmA, tmB, p));                                         \
   } while (0)
 #define AY_LAUNCH3(GG, FF, SS) AY_LAUNCH4(GG, FF, SS, false)
   if (p.tf32) {

@@ -135,8 +135,7 @@ struct Layer {
   int plane_mode = 0;               // conv: 1 = rows and planes, 2 = planes only (nothing else reads the rows)
   float* raw_f32 = nullptr;         // reference path scratch for heads
   // tmA: a_rows x 64-channel box of the input (or parity planes); tmB: BN/2 x 64 box of the weights
-  CUtensorMap tmA, tmB, tmOut;      // tmOut: 32-row x 32-channel boxes of the output rows (layers with staged TMA stores)
-  bool tma_store = false;           // row-mode layer with tiles of <= 4 chunks: epilogue stores through shared-memory boxes
+  CUtensorMap tmA, tmB;
   // yolo
   int dec_row_off = 0;
   // route copy fallback
@@ -656,14 +655,6 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     if (L.is_head) L.BN = cout_p <= 256 ? cout_p : 256;
     else L.BN = (cout_p % 256 == 0) ? 256 : (cout_p % 128 == 0) ? 128 : (cout_p % 64 == 0) ? 64 : 32;
     L.cout_rows = ay::round_up(cout_p, L.BN);
-    // Staged TMA stores: row-mode outputs (no parity planes, no fused upsample) of layers whose tile is at most four
-    // 32-column chunks - there the register epilogue's 256-bit row accesses keep L1TEX busier than the tensor pipe
-    // (opt-in, AY_TMASTORE=1: measured on the B200 it changes no layer by more than +-3 % except layer 5, which loses a
-    // pipeline stage to the boxes - profiles/r2_ab_tma_store.txt; the stores were not what held these epilogues back)
-    if (!L.first && !L.is_head && L.plane_consumer < 0 && L.up_consumer < 0 && L.BN <= 128 && getenv("AY_TMASTORE")) {
-      L.tma_store = true;
-      L.head_stage_bytes = 4096;          // two 32 x 64-byte boxes per epilogue warp
-    }
     if (L.is_head && cout_p == 32 && !getenv("AY_NO_HEADSTAGE")) {
       const ay_layer_desc& Y = Ls[L.yolo_layer].d;
       L.head_stage_bytes = (Y.n_anchors * 32 * (5 + Y.classes) * 4 + 15) & ~15;
@@ -720,11 +711,6 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       else AY_TRY(ay::make_map_2d(&L.tmA, L.planes, L.cin_p, 4 * L.plane_rows, L.cin_p, 64, L.a_rows, ctx->is_fp16));
     } else {
       AY_TRY(ay::make_map_2d(&L.tmA, in.ptr, L.cin_p, in.rows_alloc, in.pitch, 64, L.a_rows, ctx->is_fp16));
-    }
-    L.tmOut = L.tmA;
-    if (L.tma_store) {
-      const ActView& tgt = L.fused_shortcut >= 0 ? Ls[L.fused_shortcut].out : L.out;
-      AY_TRY(ay::make_map_2d(&L.tmOut, tgt.ptr, tgt.Cp, tgt.rows_alloc, tgt.pitch, 32, 32, ctx->is_fp16));
     }
     if (L.is_head)
       AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.raw_f32),
@@ -980,7 +966,7 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
           g.out_ptr = L.f_out; g.out_pitch = L.C;
           g.err_flag = ctx->err_flag;
           g.pdl = 0;
-          AY_TRY(ay::launch_conv_gemm(L.tmA, L.tmB, L.tmA, g, L.G, 2, ctx->num_sms, st));
+          AY_TRY(ay::launch_conv_gemm(L.tmA, L.tmB, g, L.G, 2, ctx->num_sms, st));
           ++ctx->launches;
           break;
         }
@@ -1154,9 +1140,9 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
   q.err_flag = ctx->err_flag;
   q.prof = ((ctx->profiling || ctx->stamping) && ctx->prof_counters) ? ctx->prof_counters + (size_t)i * ay::kProfWords : nullptr;
   q.pdl = ctx->pdl ? 1 : 0;
-  q.head_stage_bytes = L.head_stage_bytes;       // per epilogue warp: decoded-row staging (heads) or the TMA store boxes
   if (L.is_head) {
     q.head = 1;
+    q.head_stage_bytes = L.head_stage_bytes;
     q.cand_idx = ctx->cand_idx; q.cand_count = ctx->cand_count; q.cand_cap = ctx->cand_cap; q.conf_thres = ctx->cand_thres;
     q.head_fast = (ctx->dec_cols == 7 && Y->d.n_anchors == 3 && L.C == 21 && L.BN == 32 && L.cout_rows == 32 &&
                    L.m_batch == 1 && !ctx->no_head_fast) ? 1 : 0;
@@ -1188,8 +1174,7 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
     }
   }
   ++ctx->launches;
-  q.tma_store = L.tma_store ? 1 : 0;
-  return ay::launch_conv_gemm(L.tmA, L.tmB, L.tmOut, q, L.G, ctx->is_fp16, ctx->num_sms, st);
+  return ay::launch_conv_gemm(L.tmA, L.tmB, q, L.G, ctx->is_fp16, ctx->num_sms, st);
 }
 
 }  // namespace

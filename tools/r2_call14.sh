@@ -1,7 +1,7 @@
 #!/bin/bash
 O=gpurun_out/c14
 mkdir -p $O
-timeout 600 python -m pytest tests -m gpu -q -x -k "caa or plan_variants or layers" > $O/tests.log 2>&1; echo tests=$?
+timeout 600 python -m pytest tests -m gpu -q -x -k "caa or test_gpu_parity" > $O/tests.log 2>&1; echo tests=$?
 grep -E "passed|failed|FAILED|Error|^E " $O/tests.log | head
 timeout 300 python tools/layer_times.py --batch 256 --reps 5 --counters --out $O/lt.txt > $O/lt.log 2>&1; echo lt=$?
 head -12 $O/lt.txt; grep -A1 "cycle counters" $O/lt.txt | tail -1; grep -E "sum us|whole" $O/lt.txt
