@@ -9,7 +9,8 @@ whose sigmoid CAA score is <= 0.5 is dropped (``core.py:425-452``).
 Here the network runs inside the same engine as the detector: the convolutions are the tcgen05 implicit-GEMM kernel
 with a ReLU epilogue (``leaky = 2``), the pooling is the engine's 2x2 max-pool, the classifier is the ``AY_LINEAR``
 output layer, and all crops of a tile go through in one batch instead of one ``model(...)`` call per box.
-PyTorch allocates the buffers and slices the crops; there is no CPU or PyTorch fallback for the network.
+The crops are cut and normalised by one gather kernel (``ay_crop_normalize``).  PyTorch only allocates the buffers;
+there is no CPU or PyTorch fallback.
 """
 import ctypes
 
@@ -167,13 +168,25 @@ def get256Img(img, bbox_coord):
 def normalised_crops(tile, windows, mean, std):
     """``core.py:214-217`` for a list of windows at once: uint8 RGB tile [H,W,3] on the GPU -> [n,3,256,256] fp32,
     ToTensor (``/255``) then Normalize (``- mean``, ``/ std``) with the same fp32 operation order as torchvision, so the
-    network input carries the reference's bits."""
+    network input carries the reference's bits.  One launch of ``ay_crop_normalize``; there is no CPU path."""
+    if not (torch.is_tensor(tile) and tile.is_cuda and tile.dtype == torch.uint8 and tile.dim() == 3 and tile.shape[2] == 3
+            and tile.stride(2) == 1 and tile.stride(1) == 3):
+        raise ValueError("expected a CUDA uint8 tile [H,W,3] with packed pixels")
     dev = tile.device
-    crops = torch.stack([tile[yt:yb, xl:xr] for xl, xr, yt, yb in windows])                  # [n,256,256,3] uint8
-    x = crops.permute(0, 3, 1, 2).to(torch.float32).div(255)
-    m = torch.as_tensor(mean, dtype=torch.float32, device=dev).view(1, -1, 1, 1)
-    s = torch.as_tensor(std, dtype=torch.float32, device=dev).view(1, -1, 1, 1)
-    return x.sub_(m).div_(s).contiguous()
+    n = len(windows)
+    for xl, xr, yt, yb in windows:
+        if xr - xl != CROP or yb - yt != CROP:
+            raise ValueError("window (%d, %d, %d, %d) is not %d x %d" % (xl, xr, yt, yb, CROP, CROP))
+    win = torch.tensor(windows, dtype=torch.int32).reshape(n, 4).to(dev)
+    out = torch.empty((n, 3, CROP, CROP), dtype=torch.float32, device=dev)
+    m = (ctypes.c_float * 3)(*[float(v) for v in mean])
+    s = (ctypes.c_float * 3)(*[float(v) for v in std])
+    lib, ctx = _lib.load(), _lib.context(dev.index)
+    with torch.cuda.device(dev):
+        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(lib.ay_crop_normalize(ctx, ctypes.c_void_p(tile.data_ptr()), tile.shape[0], tile.shape[1], tile.stride(0),
+                                         ctypes.c_void_p(win.data_ptr()), n, CROP, m, s, ctypes.c_void_p(out.data_ptr()), st))
+    return out
 
 
 def class_preds(img_256, model, norm, device=None):
@@ -187,9 +200,9 @@ def class_preds(img_256, model, norm, device=None):
         crops = crops.unsqueeze(0)
     if crops.dtype != torch.uint8 or tuple(crops.shape[1:]) != (CROP, CROP, 3):
         raise ValueError("expected uint8 RGB crops [n,256,256,3], got %s %s" % (tuple(crops.shape), crops.dtype))
-    crops = crops.to(eng.device)
-    windows = [(0, CROP, 0, CROP)]
-    x = torch.cat([normalised_crops(c, windows, norm["mean"], norm["std"]) for c in crops])
+    crops = crops.to(eng.device).contiguous()
+    tall = crops.reshape(-1, CROP, 3)                      # the stack as one tall tile: crop i is rows [256 i, 256 (i+1))
+    x = normalised_crops(tall, [(0, CROP, CROP * i, CROP * (i + 1)) for i in range(len(crops))], norm["mean"], norm["std"])
     logits = eng.forward_nchw(x).reshape(len(crops), -1)
     eng.check()
     preds = [tuple(p) for p in torch.sigmoid(logits).cpu().tolist()]

@@ -9,6 +9,7 @@
 //   ref_conv        CUDA-core direct convolution, test cross-check of the tcgen05 kernel
 //   decode          stand-alone YOLO decode (models.py:137-169) used with ref_conv
 //   linear          fully connected output layer of the CAA filter network (core.py:161-205)
+//   crop_normalize  256^2 crops of a tile + ToTensor + Normalize for the CAA filter (core.py:109-159, 214-217)
 //   wsi_gather      slide in HBM -> the 416^2 detector inputs of its 1536^2 tiles (crop.py:13-25 + the resize)
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -502,6 +503,40 @@ int launch_wsi_gather(const uint8_t* wsi, int height, int width, long long pitch
                       int n_cols, uint8_t* out, int background, cudaStream_t s) {
   const long long total = (long long)n_rows * n_cols * S * S;
   wsi_gather_kernel<<<grid_for(total), 256, 0, s>>>(wsi, height, width, pitch, T, S, row0, col0, n_rows, n_cols, out, background);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+// ---------------------------------------------------------------- CAA filter input (core.py:109-159, 214-217, 435)
+// get256Img + ToTensor + Normalize for all boxes of a tile at once: window w = (x_left, x_right, y_top, y_bottom) of the
+// uint8 RGB tile -> out[w, c, y, x] = (tile[y_top + y, x_left + x, c] / 255 - mean[c]) / std[c], every operation one fp32
+// rounding in torchvision's order (div, sub, div), so the network sees the reference's bits.
+namespace {
+__global__ void __launch_bounds__(256)
+crop_normalize_kernel(const uint8_t* __restrict__ tile, int height, int width, long long pitch, const int32_t* __restrict__ windows,
+                      int n, int crop, float m0, float m1, float m2, float s0, float s1, float s2, float* __restrict__ out) {
+  const long long total = (long long)n * crop * crop;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(i % crop), y = (int)((i / crop) % crop), w = (int)(i / ((long long)crop * crop));
+    const int gx = __ldg(windows + 4 * w) + x, gy = __ldg(windows + 4 * w + 2) + y;
+    float r = 0.f, g = 0.f, b = 0.f;
+    if (gx >= 0 && gx < width && gy >= 0 && gy < height) {
+      const uint8_t* src = tile + gy * pitch + (long long)gx * 3;
+      r = (float)__ldg(src); g = (float)__ldg(src + 1); b = (float)__ldg(src + 2);
+    }
+    float* o = out + (size_t)w * 3 * crop * crop + (size_t)y * crop + x;
+    o[0] = __fdiv_rn(__fsub_rn(__fdiv_rn(r, 255.0f), m0), s0);
+    o[(size_t)crop * crop] = __fdiv_rn(__fsub_rn(__fdiv_rn(g, 255.0f), m1), s1);
+    o[(size_t)2 * crop * crop] = __fdiv_rn(__fsub_rn(__fdiv_rn(b, 255.0f), m2), s2);
+  }
+}
+}  // namespace
+
+int launch_crop_normalize(const uint8_t* tile, int height, int width, long long pitch, const int32_t* windows, int n, int crop,
+                          const float* mean3, const float* std3, float* out, cudaStream_t s) {
+  const long long total = (long long)n * crop * crop;
+  crop_normalize_kernel<<<grid_for(total), 256, 0, s>>>(tile, height, width, pitch, windows, n, crop, mean3[0], mean3[1], mean3[2],
+                                                        std3[0], std3[1], std3[2], out);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

@@ -175,6 +175,8 @@ struct DecodeParams {
   int lo, hi;            // zero pixels before / after each row and column of `raw`'s padded grid
 };
 int launch_decode(const DecodeParams& p, cudaStream_t s);
+int launch_crop_normalize(const uint8_t* tile, int height, int width, long long pitch, const int32_t* windows, int n, int crop,
+                          const float* mean3, const float* std3, float* out, cudaStream_t s);
 int launch_wsi_gather(const uint8_t* wsi, int height, int width, long long pitch, int T, int S, int row0, int col0, int n_rows,
                       int n_cols, uint8_t* out, int background, cudaStream_t s);
 // fully connected output layer over a zero-haloed NHWC activation (16-bit: elem_bytes 2, fp32: 4); w [O][H*W*C] in

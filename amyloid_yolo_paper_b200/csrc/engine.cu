@@ -1455,6 +1455,20 @@ extern "C" int ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* c
                                   static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int ay_crop_normalize(ay_ctx* ctx, const uint8_t* tile, int height, int width, long long pitch_bytes,
+                                 const int32_t* windows, int n, int crop, const float* mean3_h, const float* std3_h, float* out,
+                                 void* stream) {
+  AY_ENTER(ctx);
+  if (!tile || !windows || !mean3_h || !std3_h || !out || height < 1 || width < 1 || pitch_bytes < 3LL * width || n < 1 || crop < 1) {
+    set_error("ay_crop_normalize: bad arguments (tile %dx%d pitch %lld, %d windows of %d)", height, width, pitch_bytes, n, crop);
+    return AY_EINVAL;
+  }
+  for (int c = 0; c < 3; ++c)
+    if (!(std3_h[c] != 0.0f)) { set_error("ay_crop_normalize: std[%d] is zero", c); return AY_EINVAL; }
+  return ay::launch_crop_normalize(tile, height, width, pitch_bytes, windows, n, crop, mean3_h, std3_h, out,
+                                   static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int ay_wsi_gather(ay_ctx* ctx, const uint8_t* wsi, int height, int width, long long pitch_bytes, int tile_size,
                              int out_size, int row0, int col0, int n_rows, int n_cols, uint8_t* out, int background,
                              void* stream) {

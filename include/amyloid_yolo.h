@@ -144,6 +144,14 @@ int  ay_rescale_merge(ay_ctx* ctx, const float* rows, const int32_t* counts, int
  * the reference's tile files is not reproduced.                                        */
 int  ay_wsi_gather(ay_ctx* ctx, const uint8_t* wsi, int height, int width, long long pitch_bytes, int tile_size,
                    int out_size, int row0, int col0, int n_rows, int n_cols, uint8_t* out, int background, void* stream);
+/* Inputs of the CAA filter network for all boxes of one tile: get256Img (core.py:109-159) + ToTensor + Normalize
+ * (core.py:214-217, 435).  tile: [height, width, 3] uint8 RGB in device memory; windows: device int32 [n, 4] =
+ * (x_left, x_right, y_top, y_bottom) per box, as get256Img slices them (the branch logic stays on the host,
+ * caa.crop_window); mean3_h / std3_h: host fp32.  out: device fp32 [n, 3, crop, crop] with the bits of the reference's transforms
+ * (x / 255, - mean, / std, one fp32 rounding each) - the AY_IN_F32_NCHW input of the network built from AY_LINEAR.  */
+int  ay_crop_normalize(ay_ctx* ctx, const uint8_t* tile, int height, int width, long long pitch_bytes,
+                       const int32_t* windows, int n, int crop, const float* mean3_h, const float* std3_h, float* out,
+                       void* stream);
 /* bbox_iou (utils/utils.py:202-232, x1y1x2y2=True): iou[i] of box1[i or 0] vs box2[i]. */
 int  ay_bbox_iou(ay_ctx* ctx, const float* box1, int n1, const float* box2, int n2,
                  float* out_iou, void* stream);

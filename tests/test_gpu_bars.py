@@ -558,6 +558,13 @@ def test_caa_filter_end_to_end_vs_oracle(dev):
                          float(rng.uniform(0.5, 1)), cls])
     dets.append(list(dets[5]))                                              # an exact duplicate row
     dets = torch.tensor(dets, dtype=torch.float32)
+    # the crop + ToTensor + Normalize kernel returns torchvision's bits (golden norm_sum pins the oracle's to the reference's)
+    wins = [caa.crop_window(b) for b in BOXES]
+    x_gpu = caa.normalised_crops(torch.from_numpy(tile).to(dev), wins, norm["mean"], norm["std"]).cpu()
+    x_ref = torch.stack([R.caa_normalise(tile[yt:yb, xl:xr], norm["mean"], norm["std"]) for xl, xr, yt, yb in wins])
+    assert np.array_equal(bits(x_gpu.numpy()), bits(x_ref.numpy()))
+    p1 = caa.class_preds(tile[0:256, 0:256], None if False else caa.Net(), norm, device=dev)      # untrained net: shape only
+    assert len(p1) == 3 and all(0.0 <= v <= 1.0 for v in p1)
     net = caa.Net()                                                         # fp32 mode
     net.load_state_dict(state)
     got, scores = caa.filterDetectionsByCAAModel(torch.from_numpy(tile), dets, CLASSES, model=net, norm=norm,
