@@ -19,6 +19,7 @@
 //   cluster : one warp per keeper: ordered member list, ATen-order weighted sums
 #include "ay_common.h"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace ay {
@@ -63,6 +64,31 @@ __device__ __forceinline__ float iou_xyxy(const float4 a, const float4 b) {
   const float aa = __fmul_rn(__fadd_rn(__fsub_rn(a.z, a.x), 1.0f), __fadd_rn(__fsub_rn(a.w, a.y), 1.0f));
   const float ab = __fmul_rn(__fadd_rn(__fsub_rn(b.z, b.x), 1.0f), __fadd_rn(__fsub_rn(b.w, b.y), 1.0f));
   return __fdiv_rn(inter, __fadd_rn(__fsub_rn(__fadd_rn(aa, ab), inter), 1e-16f));
+}
+
+// (b.z - b.x + 1) * (b.w - b.y + 1), the roundings of utils/utils.py:227-228
+__device__ __forceinline__ float box_area(const float4 b) {
+  return __fmul_rn(__fadd_rn(__fsub_rn(b.z, b.x), 1.0f), __fadd_rn(__fsub_rn(b.w, b.y), 1.0f));
+}
+
+// iou_xyxy(a, b) > thr with the SAME truth value as the rounded division of the reference, but the division is only
+// carried out when a fast quotient (error below 1e-6 relative) lands within 1e-4 of the threshold: disjoint boxes have
+// iou = 0 (never above a threshold >= 0), and for every other pair the approximate quotient decides unless it is that
+// close.  The mask kernel evaluates n^2 / 2 pairs per tile (57 M at 10 647 candidates): this is its inner loop.
+__device__ __forceinline__ bool iou_above(const float4 a, const float aa, const float4 b, const float ab, const float thr) {
+  const float iw = __fadd_rn(__fsub_rn(fminf(a.z, b.z), fmaxf(a.x, b.x)), 1.0f);
+  const float ih = __fadd_rn(__fsub_rn(fminf(a.w, b.w), fmaxf(a.y, b.y)), 1.0f);
+  // disjoint (or NaN) boxes: clamp(min=0) makes one factor of the intersection 0, the quotient is 0 or NaN, and neither is
+  // above a threshold >= 0 (the caller takes the plain path for a negative threshold)
+  if (!(iw > 0.0f) || !(ih > 0.0f)) return false;
+  const float inter = __fmul_rn(iw, ih);
+  const float denom = __fadd_rn(__fsub_rn(__fadd_rn(aa, ab), inter), 1e-16f);
+  if (denom < 1e30f) {                                   // (__fdividef is only specified below 2^126; NaN fails the test)
+    const float q = __fdividef(inter, denom);            // at most 2 ulp from the true quotient
+    if (q > thr * 1.0001f + 1e-30f) return true;
+    if (q < thr * 0.9999f) return false;
+  }
+  return __fdiv_rn(inter, denom) > thr;
 }
 
 // ------------------------------------------------------------------ prepare
@@ -170,7 +196,7 @@ nms_prepare_kernel(float* __restrict__ pred, int n, int n_classes, float conf_th
 
 // ------------------------------------------------------------------ mask
 __global__ void __launch_bounds__(64)
-nms_mask_kernel(int n, float nms_thres, uint8_t* scratch, NmsLayout L) {
+nms_mask_kernel(int n, float nms_thres, uint8_t* scratch, NmsLayout L, int plain) {
   const int b = blockIdx.y;
   const int cnt = reinterpret_cast<const int*>(scratch + L.count)[b];
   const int nb = (cnt + 63) >> 6;
@@ -179,6 +205,7 @@ nms_mask_kernel(int n, float nms_thres, uint8_t* scratch, NmsLayout L) {
   const int* cls = reinterpret_cast<const int*>(scratch + L.cls) + (size_t)b * n;
   unsigned long long* mask = reinterpret_cast<unsigned long long*>(scratch + L.mask) + (size_t)b * n * L.words;
   __shared__ float4 cbox[64];
+  __shared__ float carea[64];
   __shared__ int ccls[64];
   for (long long pi = blockIdx.x; pi < pairs; pi += gridDim.x) {
     // linear index over the upper triangle (rb <= cb), row-major
@@ -189,18 +216,25 @@ nms_mask_kernel(int n, float nms_thres, uint8_t* scratch, NmsLayout L) {
     const int j0 = cb * 64;
     __syncthreads();
     if (j0 + (int)threadIdx.x < cnt) {
-      cbox[threadIdx.x] = box[j0 + threadIdx.x];
+      const float4 bj = box[j0 + threadIdx.x];
+      cbox[threadIdx.x] = bj;
+      carea[threadIdx.x] = box_area(bj);
       ccls[threadIdx.x] = cls[j0 + threadIdx.x];
     }
     __syncthreads();
     const int i = rb * 64 + threadIdx.x;
     if (i < cnt) {
       const float4 bi = box[i];
+      const float ai = box_area(bi);
       const int ci = cls[i];
       const int lim = min(64, cnt - j0);
       unsigned long long bits = 0;
-      for (int j = 0; j < lim; ++j) {
-        if (ccls[j] == ci && iou_xyxy(bi, cbox[j]) > nms_thres) bits |= (1ull << j);
+      if (nms_thres >= 0.0f && !plain) {
+        for (int j = 0; j < lim; ++j)
+          if (ccls[j] == ci && iou_above(bi, ai, cbox[j], carea[j], nms_thres)) bits |= (1ull << j);
+      } else {
+        for (int j = 0; j < lim; ++j)
+          if (ccls[j] == ci && iou_xyxy(bi, cbox[j]) > nms_thres) bits |= (1ull << j);
       }
       mask[(size_t)i * L.words + cb] = bits;
     }
@@ -225,13 +259,26 @@ nms_sweep_kernel(int n, uint8_t* scratch, NmsLayout L) {
     const int wi = i >> 6;
     if ((removed[wi] >> (i & 63)) & 1ull) continue;     // warp-uniform (shared memory broadcast)
     int pc = 0;
-    for (int w = wi + lane; w < nw; w += 32) {
-      unsigned long long m = mask[(size_t)i * L.words + w];
-      if (w == wi) m &= ~((1ull << (i & 63)) - 1ull);    // only rows >= i are still in play
-      m &= ~removed[w];
-      removed[w] |= m;
-      mask[(size_t)i * L.words + w] = m;                  // row i now holds its cluster members
-      pc += __popcll(m);
+    // all words of the row first (up to kMaxRows / 64 / 32 = 8 per lane, independent loads: one memory round trip per
+    // surviving row instead of one per 32 words - the walk is serial, so this latency is the kernel's time)
+    unsigned long long mw[kMaxRows / 64 / 32];
+    unsigned long long* mrow = mask + (size_t)i * L.words;
+#pragma unroll
+    for (int k = 0; k < kMaxRows / 64 / 32; ++k) {
+      const int w = wi + lane + 32 * k;
+      mw[k] = w < nw ? mrow[w] : 0ull;
+    }
+#pragma unroll
+    for (int k = 0; k < kMaxRows / 64 / 32; ++k) {
+      const int w = wi + lane + 32 * k;
+      if (w < nw) {
+        unsigned long long m = mw[k];
+        if (w == wi) m &= ~((1ull << (i & 63)) - 1ull);    // only rows >= i are still in play
+        m &= ~removed[w];
+        removed[w] |= m;
+        mrow[w] = m;                                        // row i now holds its cluster members
+        pc += __popcll(m);
+      }
     }
     for (int o = 16; o > 0; o >>= 1) pc += __shfl_xor_sync(0xffffffffu, pc, o);
     if (lane == 0) { keep_pos[nkeep] = i; keep_off[nkeep] = running; }
@@ -426,7 +473,8 @@ int launch_nms(float* pred, int batch, int n_rows, int n_classes, float conf_thr
                                                             cand_cap);
   AY_CUDA(cudaGetLastError());
   if (ev) AY_CUDA(cudaEventRecord(ev[1], s));
-  nms_mask_kernel<<<dim3(96, batch), 64, 0, s>>>(n_rows, nms_thres, sc, L);
+  // AY_NMS_PLAIN=1 (tests): every pair through the rounded division instead of the fast quotient with exact fallback
+  nms_mask_kernel<<<dim3(96, batch), 64, 0, s>>>(n_rows, nms_thres, sc, L, getenv("AY_NMS_PLAIN") ? 1 : 0);
   AY_CUDA(cudaGetLastError());
   if (ev) AY_CUDA(cudaEventRecord(ev[2], s));
   nms_sweep_kernel<<<batch, 32, 0, s>>>(n_rows, sc, L);

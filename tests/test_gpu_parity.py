@@ -139,6 +139,48 @@ def test_nms_edge_cases():
     assert out[0].shape[0] == 1 and out[0][0, 4] == 0.5
 
 
+@pytest.mark.parametrize("thr", [0.5, 1.0 / 3.0, 0.25, 0.4, 0.0])
+def test_nms_iou_exactly_at_the_threshold(thr):
+    """The mask kernel decides most pairs with a fast quotient and divides only near the threshold; the truth value must be
+    that of the reference's rounded division (`> nms_thres`, utils/utils.py:259).  Integer boxes whose IoU is a small
+    rational: many pairs sit EXACTLY on 1/2, 1/3, 1/4 (not above: no merge), one ulp-level neighbour on either side, plus
+    disjoint and touching pairs (the +1 of utils.py:221-222 gives touching boxes a positive intersection)."""
+    from amyloid_yolo_paper_b200.utils.utils import non_max_suppression
+    rng = np.random.default_rng(int(thr * 1000))
+    rows = []
+    for k in range(400):
+        x0, y0 = rng.integers(0, 300, 2)
+        w, h = rng.integers(4, 40, 2)
+        # xyxy boxes with inclusive-pixel sizes (w, h): a partner covering a 1/2, 1/3, 1/4 ... share, shifted copies, neighbours
+        base = [x0, y0, x0 + w - 1, y0 + h - 1]
+        partner = [x0, y0, x0 + w - 1, y0 + int(h * rng.integers(1, 5)) - 1]
+        dx = int(rng.integers(0, w + 2))
+        shifted = [x0 + dx, y0, x0 + dx + w - 1, y0 + h - 1]
+        for bx in (base, partner, shifted):
+            x1, y1, x2, y2 = [float(v) for v in bx]
+            rows.append([(x1 + x2) / 2, (y1 + y2) / 2, x2 - x1, y2 - y1, float(rng.uniform(0.6, 1.0)), 0.9, 0.1])
+    P = np.asarray(rows, np.float32)[None]
+    # xywh -> xyxy in fp32 must give back the integer corners for the ties to be exact
+    assert np.array_equal(R.xywh2xyxy(P[0, :, :4]), np.round(R.xywh2xyxy(P[0, :, :4])))
+    out, keep = non_max_suppression(torch.from_numpy(P.copy()), 0.5, thr, return_keep=True)
+    want, kidx = R.nms_exact(P[0], 0.5, thr)
+    assert keep[0].tolist() == kidx.tolist()
+    assert np.array_equal(bits(out[0]), bits(want))
+    os.environ["AY_NMS_PLAIN"] = "1"                   # every pair through the rounded division: the same bits
+    try:
+        out2, keep2 = non_max_suppression(torch.from_numpy(P.copy()), 0.5, thr, return_keep=True)
+    finally:
+        del os.environ["AY_NMS_PLAIN"]
+    assert keep2[0].tolist() == kidx.tolist() and np.array_equal(bits(out2[0]), bits(want))
+    # the construction does put pairs on the threshold
+    xy = R.xywh2xyxy(P[0, :, :4])
+    iou = R.bbox_iou_xyxy(xy[0], xy[:3])
+    assert iou[0] == 1.0
+    if thr in (0.5, 0.25) or abs(thr - 1 / 3) < 1e-9:
+        ties = sum(int((R.bbox_iou_xyxy(xy[3 * k], xy[3 * k + 1:3 * k + 2]) == np.float32(thr)).sum()) for k in range(400))
+        assert ties > 20, ties
+
+
 def test_nms_capacity_overflow_is_loud(dev):
     from amyloid_yolo_paper_b200 import _lib, synth
     from amyloid_yolo_paper_b200.utils.utils import non_max_suppression_device
