@@ -107,10 +107,16 @@ class CAAEngine(Engine):
         self.img_size = CROP
         self.in_channels = 3
         n = 13
+        # fp32 mode: the tensor-core convolution (3 x tf32) needs channel counts that are multiples of 32; 16, 48 and 80
+        # are padded with zero filters (ReLU(0 + 0) = 0 feeds zero weights of the next stage: the same values, and stages
+        # 2-6 leave the CUDA-core kernel).  The 16-bit path pads its buffers to 32 channels by itself.
+        chans = list(CHANNELS)
+        if precision == "fp32":
+            chans = [3] + [-(-c // 32) * 32 for c in CHANNELS[1:]]
         descs = (_lib.LayerDesc * n)()
         for k in range(6):
             conv, pool = descs[2 * k], descs[2 * k + 1]
-            conv.type, conv.filters, conv.size, conv.stride, conv.leaky = _lib.AY_CONV, CHANNELS[k + 1], 3, 1, 2
+            conv.type, conv.filters, conv.size, conv.stride, conv.leaky = _lib.AY_CONV, chans[k + 1], 3, 1, 2
             pool.type, pool.size, pool.stride = _lib.AY_MAXPOOL, 2, 2
         descs[12].type, descs[12].filters = _lib.AY_LINEAR, int(num_classes)
         self.ctx = ctypes.c_void_p()
@@ -122,6 +128,12 @@ class CAAEngine(Engine):
             _lib.check(self.lib.ay_net_build(self.ctx, descs, n, 3, CROP, self.max_batch, dtype))
             for k in range(6):
                 w, b = fold_stage(state_dict, k)
+                if w.shape[:2] != (chans[k + 1], chans[k]):
+                    wp = np.zeros((chans[k + 1], chans[k], 3, 3), dtype=np.float32)
+                    wp[:w.shape[0], :w.shape[1]] = w
+                    bp = np.zeros((chans[k + 1],), dtype=np.float32)
+                    bp[:b.shape[0]] = b
+                    w, b = wp, bp
                 _lib.check(self.lib.ay_net_set_conv(self.ctx, 2 * k, P(w), P(b)))
             w = np.ascontiguousarray(state_dict["classifier.0.weight"].detach().to("cpu", torch.float32).numpy())
             b = np.ascontiguousarray(state_dict["classifier.0.bias"].detach().to("cpu", torch.float32).numpy())
