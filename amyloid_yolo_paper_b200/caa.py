@@ -278,3 +278,37 @@ def filterDetectionsByCAAModel(img_name, detections, classes, model=None, norm=N
     kept = [list(row) for row, s in zip(rows, scores) if not (classes[int(row[6])] == "CAA" and s[2] <= 0.5)]
     out = torch.as_tensor(kept)
     return (out, [tuple(s) for s in scores]) if return_scores else out
+
+
+def filter_batch(tiles, detections_list, classes, model, norm, device=None):
+    """``filterDetectionsByCAAModel`` for a batch of tiles in one pass: ``tiles`` uint8 ``[B,H,H,3]`` (host or device),
+    ``detections_list`` the per-tile ``[k,7]`` tensors (or None) of ``TileDetector.detect``.  The distinct boxes of ALL
+    tiles go through ``ay_crop_normalize`` and the network together (the batch is addressed as one tall tile), so the
+    per-call cost of the single-tile form is paid once per batch.  Returns, per tile, what the single-tile call returns
+    (same rows, same set order)."""
+    eng = model.engine(device)
+    tiles = torch.as_tensor(tiles)
+    if tiles.dim() != 4 or tiles.shape[3] != 3 or tiles.dtype != torch.uint8 or tiles.shape[1] != tiles.shape[2]:
+        raise ValueError("expected uint8 tiles [B,H,H,3], got %s %s" % (tuple(tiles.shape), tiles.dtype))
+    if len(detections_list) != tiles.shape[0]:
+        raise ValueError("%d detection lists for %d tiles" % (len(detections_list), tiles.shape[0]))
+    size = tiles.shape[1]
+    tall = tiles.to(eng.device, non_blocking=True).contiguous().reshape(-1, size, 3)
+    rows_of, windows = [], []
+    for b, det in enumerate(detections_list):
+        rows = [] if det is None else list(set(tuple(entry) for entry in det.tolist()))
+        rows_of.append(rows)
+        for x1, y1, x2, y2, _, _, _ in rows:
+            xl, xr, yt, yb = crop_window((int(x1), int(y1), int(x2 - x1), int(y2 - y1)), size)
+            windows.append((xl, xr, yt + b * size, yb + b * size))
+    scores = []
+    for lo in range(0, len(windows), eng.max_batch):
+        x = normalised_crops(tall, windows[lo:lo + eng.max_batch], norm["mean"], norm["std"])
+        scores += torch.sigmoid(eng.forward_nchw(x).reshape(x.shape[0], -1)).cpu().tolist()
+    eng.check()
+    out, at = [], 0
+    for rows in rows_of:
+        s = scores[at:at + len(rows)]
+        at += len(rows)
+        out.append(torch.as_tensor([list(r) for r, sc in zip(rows, s) if not (classes[int(r[6])] == "CAA" and sc[2] <= 0.5)]))
+    return out

@@ -75,10 +75,11 @@ def evaluate(model, path, iou_thres, conf_thres, nms_thres, img_size, batch_size
 
 
 def run_model_on_validation_images(model, image_folder, classes, conf_thres=0.8, nms_thres=0.4, img_size=416, batch_size=8,
-                                   n_cpu=12, merge_boxes=True, strip_prefix=None):
+                                   n_cpu=12, merge_boxes=True, strip_prefix=None, caa_model=None, caa_norm=None):
     """The dictionary ``prospective.runModelOnValidationImages`` pickles (``prospective.py:84-92``): image name ->
     list of ``({'x1','x2','y1','y2','conf','cls_conf','cls_pred'}, class name)``; images without detections map to an
-    empty list.  (The consensus CAA filter that follows in the reference is outside this build)"""
+    empty list.  With ``caa_model`` (a ``caa.Net``) and ``caa_norm`` the consensus CAA filter runs on every image's merged
+    detections as in ``prospective.py:86-87`` (rows then come in the filter's set order, as in the reference)."""
     device = torch.device("cuda", torch.cuda.current_device())
     det = TileDetector(model, conf_thres=conf_thres, nms_thres=nms_thres, merge_boxes=merge_boxes, max_batch=batch_size,
                        device=device, img_size=img_size)
@@ -96,6 +97,11 @@ def run_model_on_validation_images(model, image_folder, classes, conf_thres=0.8,
             out[key] = []
             if d is None:
                 continue
+            if caa_model is not None:
+                from .caa import filterDetectionsByCAAModel
+                d = filterDetectionsByCAAModel(p, d, classes, model=caa_model, norm=caa_norm, device=device)
+                if len(d) == 0:                           # (everything filtered: prospective.py:88-89)
+                    continue
             for x1, y1, x2, y2, conf, cls_conf, cls_pred in d:
                 out[key].append(({"x1": x1.item(), "x2": x2.item(), "y1": y1.item(), "y2": y2.item(), "conf": conf.item(),
                                   "cls_conf": cls_conf.item(), "cls_pred": cls_pred.item()}, classes[int(cls_pred)]))

@@ -505,6 +505,27 @@ def test_evaluate_and_prediction_dict(dev, tmp_path):
             assert name == ["CAA", "Cored"][int(w[6])]
             n += 1
     assert n > 10
+    # ... followed by the consensus CAA filter (prospective.py:86-87): per image, the oracle's filter on the oracle's rows
+    from PIL import Image
+    from amyloid_yolo_paper_b200 import caa
+    from oracle.make_golden_caa import NORM, seeded_caa_state
+    state = seeded_caa_state(5)
+    net = caa.Net()
+    net.load_state_dict(state)
+    filtered = run_model_on_validation_images(m, str(tmp_path / "images") + "/", ["CAA", "Cored"], batch_size=2, n_cpu=2,
+                                              caa_model=net, caa_norm=NORM)
+    dropped = 0
+    for b in range(5):
+        img = np.asarray(Image.open(str(tmp_path / "images" / ("t%d.png" % b))).convert("RGB"))
+        rows = _oracle_final(dec[b], 416, (832, 832))
+        want, logits = R.caa_filter_faithful(img, rows, ["CAA", "Cored"], state, NORM["mean"], NORM["std"], return_logits=True)
+        order = list(set(tuple(r) for r in rows.tolist()))
+        sure = {r for r, z in zip(order, logits) if abs(z) > 0.05}
+        got_rows = [tuple(np.float32(d[k]).item() for k in ("x1", "y1", "x2", "y2", "conf", "cls_conf", "cls_pred"))
+                    for d, _ in filtered["t%d.png" % b]]
+        assert [r for r in got_rows if r in sure] == [r for r in want if r in sure], b
+        dropped += len(order) - len(got_rows)
+    print("prediction dictionary with the CAA filter: %d rows dropped" % dropped)
 
 
 # ------------------------------------------------------------------ consensus CAA filter
@@ -583,6 +604,16 @@ def test_caa_filter_end_to_end_vs_oracle(dev):
     print("CAA filter: %d distinct rows, %d kept by the oracle, %d by the engine, CAA logits %.2f .. %.2f"
           % (len(order), len(want), len(got_rows), z.min(), z.max()))
     assert 3 <= dropped <= len(order) // 2
+    # the batched form: three tiles (one without detections) in one pass == the single-tile calls
+    tiles3 = torch.from_numpy(np.stack([tile, tile[::-1].copy(), tile]))
+    lists = [dets, dets[:7], None]
+    batch = caa.filter_batch(tiles3, lists, CLASSES, net, norm, device=dev)
+    for t, d, g in zip(tiles3, lists, batch):
+        if d is None:
+            assert g.numel() == 0
+            continue
+        one = caa.filterDetectionsByCAAModel(t, d, CLASSES, model=net, norm=norm, device=dev)
+        assert torch.equal(g, one)
     # nothing to filter
     empty = caa.filterDetectionsByCAAModel(torch.from_numpy(tile), torch.zeros((0, 7)), CLASSES, model=net, norm=norm, device=dev)
     assert empty.numel() == 0
