@@ -780,13 +780,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int img_first = __shfl_sync(0xffffffffu, img, lane0);     // (every lane takes part: no short-circuit around it)
         const bool one_image = __all_sync(0xffffffffu, !valid || img == img_first) != 0;
         const bool staged = p.head_stage_bytes > 0 && one_image;
+        const bool chunk_staged = staged && nchunks > 1;              // wide heads: 32 x 33 floats per warp, chunk by chunk
         float* hs = reinterpret_cast<float*>(smem_raw + (staging_base - smem_addr(smem_raw)) + (uint32_t)ew * (uint32_t)p.head_stage_bytes);
         if (p.head_fast) {
           // The shipped detector's head: 3 anchors x (5 + 2 classes) = 21 channels in ONE 32-column chunk.  Anchor and
           // field of every channel are compile-time constants here (no select chain per channel), and the two
           // transcendentals are single MUFU instructions: ex2.approx on t*log2(e) and rcp.approx, each within 2 ulp -
-          // four orders of magnitude below the 16-bit activations' own error on these outputs (the generic path below
-          // and the stand-alone decode_kernel keep expf and the IEEE division).
+          // four orders of magnitude below the 16-bit activations' own error on these outputs (the stand-alone
+          // decode_kernel of the test path keeps expf and the IEEE division).
           uint32_t v[32];
           tmem_load32(t_acc, v);
           const float fgx = (float)gx, fgy = (float)gy;
@@ -827,8 +828,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int ch = ch0 + j;
             const bool wh = (fj == 2) | (fj == 3);
             const float t = __uint_as_float(v[j]) + s_bias[ch];
-            const float e = (p.dbg & 512) ? t : expf(wh ? t : -t);          // (ablation 512: no transcendental)
-            const float sg = 1.0f / (1.0f + e);                                   // sigmoid(t), as sigmoid_acc
+            // single MUFU instructions (ex2.approx, rcp.approx: 2 ulp), as in the fast path above: with expf and the IEEE
+            // division the 255-channel heads of yolov3-tiny spent 25 k cycles per chunk here
+            const float e = (p.dbg & 512) ? t : fast_exp(wh ? t : -t);      // (ablation 512: no transcendental)
+            const float sg = fast_rcp(1.0f + e);                                  // sigmoid(t)
             const float anchor = (fj == 2) ? p.anchor_w[aj] : p.anchor_h[aj];
             const float off = (fj == 0) ? (float)gx : (float)gy;
             const float box = wh ? __fmul_rn(__fmul_rn(e, anchor), p.stride) : __fmul_rn(__fadd_rn(sg, off), p.stride);
@@ -841,6 +844,29 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             if (++fj == p.dec_cols) { fj = 0; aj = min(aj + 1, p.n_anchors - 1); }
           }
+          if (chunk_staged) {
+            // Wide heads (255 channels: 3 anchors x 85): the chunk's 32 x 32 values are transposed through shared memory
+            // (row pitch 33 floats: conflict-free both ways) and leave as one 128-byte run per valid row - lane j carries
+            // channel ch0 + j, whose (anchor, field) is fixed for the chunk - instead of 32 scalar stores per lane at a
+            // 340-byte stride.
+            if (valid) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) hs[rank_v * 33 + j] = r[j];
+            }
+            __syncwarp();
+            const int chl = ch0 + lane;
+            const int al = chl / p.dec_cols, fl = chl - al * p.dec_cols;
+            // (the shuffles are executed by every lane, outside the per-lane condition)
+            const unsigned long long first = (unsigned long long)obase;
+            const unsigned long long b64 = ((unsigned long long)__shfl_sync(0xffffffffu, (unsigned)(first >> 32), lane0) << 32) |
+                                           (unsigned long long)__shfl_sync(0xffffffffu, (unsigned)first, lane0);
+            if (chl < p.cout && !(p.dbg & 256)) {
+              float* dst = reinterpret_cast<float*>(b64) + (size_t)al * a_step + fl;
+              for (int rr = 0; rr < nvalid; ++rr) dst[(size_t)rr * p.dec_cols] = hs[rr * 33 + lane];
+            }
+            __syncwarp();
+            continue;
+          }
           int a = ch0 / p.dec_cols, fi = ch0 - a * p.dec_cols;   // running (anchor, field) of channel ch
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
@@ -851,7 +877,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (++fi == p.dec_cols) { fi = 0; ++a; }
           }
         }
-        if (staged && nvalid > 0 && !(p.dbg & 256)) {
+        if (staged && !chunk_staged && nvalid > 0 && !(p.dbg & 256)) {
           __syncwarp();
           const unsigned long long first = (unsigned long long)obase;
           const unsigned long long b64 = ((unsigned long long)__shfl_sync(0xffffffffu, (unsigned)(first >> 32), lane0) << 32) |

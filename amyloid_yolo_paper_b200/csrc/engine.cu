@@ -658,6 +658,8 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
     if (L.is_head && cout_p == 32 && !getenv("AY_NO_HEADSTAGE")) {
       const ay_layer_desc& Y = Ls[L.yolo_layer].d;
       L.head_stage_bytes = (Y.n_anchors * 32 * (5 + Y.classes) * 4 + 15) & ~15;
+    } else if (L.is_head && !getenv("AY_NO_HEADSTAGE")) {
+      L.head_stage_bytes = 32 * 33 * 4;         // wide heads (yolov3-tiny: 255 channels): a 32 x 32 transpose per warp and chunk
     }
     L.G = L.s2_packed ? 2 : (L.d.size == 3 && L.d.stride == 1 && !L.first) ? 3 : 1;
     // first layer: four 256-row blocks per tile (K is only 3 x 32: one barrier round and three loads per 1024 rows);
