@@ -572,6 +572,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int img, yy, xx;
       split_row(m, img, yy, xx);
       const bool halo = is_halo(yy, xx, p.Hp, p.Wp);
+      bool released = false;                                 // accumulator already handed back (row epilogue, last chunk)
 
       if (p.dbg & 64) {                                          // ablation: no epilogue work at all
         bar_wait(tfull_bar(acc), acc_phase, p.err_flag, 4);
@@ -695,6 +696,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (c < nchunks) {
             uint32_t v[32];
             tmem_load32(t_acc + (uint32_t)(c * 32), v);
+            if (c + c_step >= nchunks) {
+              // that was this warp's last read of the accumulator: hand it back to the MMA issuer NOW, before the last
+              // chunk's arithmetic and stores (wide tiles have two accumulators only, and the issuer was waiting 16 % of a
+              // 52^2 residual layer's time for the epilogue to let go)
+              fence_before();
+              __syncwarp();
+              if (lane == 0) bar_arrive_remote(tempty_bar(acc) & kLeaderMask);
+              released = true;
+            }
             RowTarget t = t0;
             int ch = c * 32;
             if (R > 1) {                                         // sub-block c of a row-batched tile: 128 rows further per c
@@ -890,9 +900,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
       // this warp is done reading the accumulator: one arrival per warp on the LEADER's barrier
-      fence_before();
-      __syncwarp();
-      if (lane == 0) bar_arrive_remote(tempty_bar(acc) & kLeaderMask);
+      if (!released) {
+        fence_before();
+        __syncwarp();
+        if (lane == 0) bar_arrive_remote(tempty_bar(acc) & kLeaderMask);
+      }
       // next tile of this warp
       acc += it_step;
       if (acc >= num_acc) { acc -= num_acc; acc_phase ^= 1u; }
