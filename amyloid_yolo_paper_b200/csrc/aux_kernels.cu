@@ -111,13 +111,13 @@ __global__ void first_conv_kernel(FirstConvParams p) {
 // (3 used) per pixel: 16 bytes per pixel, so that three horizontally adjacent pixels are 24 contiguous
 // elements and one TMA row of the first layer's A operand (see engine.cu, first layer).
 __global__ void prep_input_kernel(FirstConvParams p) {
+  // grid: (x blocks, padded rows, images) - no division per pixel
   const int Sp = padded(p.S);
-  const long long total = (long long)p.batch * Sp * Sp;
-  const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= total) return;
-  const int n = (int)(m / ((long long)Sp * Sp));
-  const int pix = (int)(m - (long long)n * Sp * Sp);
-  const int y = pix / Sp - kPadLo, x = pix - (pix / Sp) * Sp - kPadLo;
+  const int xp = blockIdx.x * blockDim.x + threadIdx.x;
+  if (xp >= Sp) return;
+  const int n = blockIdx.z;
+  const int y = (int)blockIdx.y - kPadLo, x = xp - kPadLo;
+  const long long m = ((long long)n * Sp + blockIdx.y) * Sp + xp;
   float v[3] = {0.f, 0.f, 0.f};
   if (y >= 0 && y < p.S && x >= 0 && x < p.S) {
     if (p.in_kind == AY_IN_F32_NCHW) {
@@ -372,8 +372,9 @@ int launch_first_conv(const FirstConvParams& p, cudaStream_t s) {
 }
 
 int launch_prep_input(const FirstConvParams& p, cudaStream_t s) {
-  const long long total = (long long)p.batch * padded(p.S) * padded(p.S);
-  prep_input_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(p);
+  const int Sp = padded(p.S);
+  if (p.batch > 65535 || Sp > 65535) { set_error("prep_input: batch %d / size %d beyond the launch grid", p.batch, p.S); return AY_EINVAL; }
+  prep_input_kernel<<<dim3((Sp + 127) / 128, Sp, p.batch), 128, 0, s>>>(p);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }
