@@ -34,7 +34,9 @@ def pack_detections(per_tile, kmax=None, device=None):
     counts = torch.tensor(ks, dtype=torch.int32)
     kmax = int(kmax if kmax is not None else (max(ks) if ks else 0))
     rows = torch.zeros((len(per_tile), max(kmax, 1), 7), dtype=torch.float32)
-    live = [d.to(torch.float32).cpu() for d in per_tile if d is not None and d.shape[0]]
+    # (detect_stream hands over fp32 CPU tensors: no per-tile conversion then - this loop runs once per tile of the sweep)
+    live = [d if (d.dtype == torch.float32 and not d.is_cuda) else d.to(torch.float32).cpu()
+            for d in per_tile if d is not None and d.shape[0]]
     if live:
         flat = torch.cat(live, 0)
         c64 = counts.to(torch.int64)
