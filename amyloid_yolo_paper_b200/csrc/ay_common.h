@@ -201,6 +201,8 @@ int launch_f32_prep(const F32PrepParams& p, cudaStream_t s);
 // in, rows of 2C floats out
 int launch_f32_split(const float* in, int in_pitch, int C, long long rows, float* out, cudaStream_t s);
 // parity planes (classic one-pixel frame) of a [B,H,W] fp32 tensor with `pitch` floats per pixel, for stride-2 convolutions
+int launch_f32_split_s2_gather(const float* in, int in_pitch, int C, int batch, int H, int W, float* planes,
+                               long long plane_rows, cudaStream_t s);
 int launch_f32_s2_gather(const float* in, int pitch, int batch, int H, int W, float* planes, long long plane_rows,
                          cudaStream_t s);
 int launch_f32_conv(const F32ConvParams& p, cudaStream_t s);

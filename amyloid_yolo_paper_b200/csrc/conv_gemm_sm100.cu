@@ -604,6 +604,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               v[e] = __float_as_uint(y);
             }
             if (store && !(p.dbg & 4)) {
+              if (has_res) {
+                // fused [shortcut] of the fp32 mode (models.py:246-248): one more fp32 rounding, as the stand-alone add
+                const float* rrow = static_cast<const float*>(p.res_ptr) + (size_t)m * p.res_pitch + n0 + c * 32;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  uint32_t r8[8];
+                  ldg256(rrow + q * 8, r8);
+#pragma unroll
+                  for (int e = 0; e < 8; ++e)
+                    v[q * 8 + e] = __float_as_uint(__fadd_rn(__uint_as_float(v[q * 8 + e]), __uint_as_float(r8[e])));
+                }
+              }
 #pragma unroll
               for (int q = 0; q < 4; ++q) stg256(orow + c * 32 + q * 8, &v[q * 8]);
             }
@@ -1023,7 +1035,7 @@ int launch_conv_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvG
   } while (0)
 #define AY_LAUNCH3(GG, FF, SS) AY_LAUNCH4(GG, FF, SS, false)
   if (p.tf32) {
-    if (p.head || p.has_res || p.b_resident || p.a_mode != 0 || p.m_batch != 1 || (G != 1 && G != 3) || p.tf32_na < 1 ||
+    if (p.head || p.b_resident || p.a_mode != 0 || p.m_batch != 1 || (G != 1 && G != 3) || p.tf32_na < 1 ||
         p.BN * p.tf32_na * p.num_acc > 512) {
       set_error("conv_gemm: tf32 mode supports plain 1x1 / 3x3 tiles only");
       return AY_EINVAL;

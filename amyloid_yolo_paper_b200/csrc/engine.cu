@@ -468,6 +468,13 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
             L.a_rows = L.G == 3 ? 130 : 128;
             L.units_per_stage = 1;
             ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, 0, 1, 0, &L.stages, &L.nbuf);
+            if (L.G == 1 && !getenv("AY_ONE_UNIT")) {
+              // 1x1 and stride-2 layers have one tap per unit (four K=8 MMAs): three consecutive units per stage amortise
+              // the stage's barrier round trip over twelve MMAs, as the three taps of a stride-1 3x3 unit do
+              int st3 = 0, nb3 = 0;
+              ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, 0, 3, 0, &st3, &nb3);
+              if (st3 >= 3) { L.units_per_stage = 3; L.stages = st3; L.nbuf = nb3; }
+            }
             if (L.stages < 2) { set_error("layer %d: tf32 tile does not fit in shared memory", i); return AY_EINVAL; }
             AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_w2), sizeof(float) * (size_t)L.C * 2 * L.ktot, true));
             const int iH = i ? Ls[i - 1].H : img_size, iW = i ? Ls[i - 1].W : img_size;
@@ -480,6 +487,15 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
           }
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_w), sizeof(float) * (size_t)L.d.size * L.d.size * L.cin * L.C, false));
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.C, true));
+          // tensor-core convolution followed by a [shortcut] and read by nothing else: the add moves into its epilogue and
+          // the convolution's own output is never stored (AY_F32_NO_RESFUSE=1: separate add, every block stored)
+          if (L.impl == 5 && i + 1 < n_layers && Ls[i + 1].d.type == AY_SHORTCUT && explicit_refs[i].empty() &&
+              Ls[i + 1].d.src[0] != i && !getenv("AY_F32_NO_RESFUSE")) {
+            L.fused_shortcut = i + 1;
+            L.residual_src = Ls[i + 1].d.src[0];
+            Ls[i + 1].fused_into_prev = true;
+            break;
+          }
           AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.f_out), sizeof(float) * elems, true));
           break;
         case AY_ROUTE:
@@ -921,11 +937,16 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
       case AY_CONV: {
         if (L.impl == 5) {
           // [hi | lo] copy of the input rows, parity planes for stride 2, then the 3-pass tf32 GEMM
-          AY_TRY(ay::launch_f32_split(prev, pC, L.cin, ay::padded_rows_f32(batch, pH, pW), ctx->f_split, st));
-          ++ctx->launches;
-          if (L.d.stride == 2) {
-            AY_TRY(ay::launch_f32_s2_gather(ctx->f_split, 2 * L.cin, batch, pH, pW, ctx->f_planes, L.plane_rows, st));
+          if (L.d.stride == 2 && !getenv("AY_F32_TWO_PASS")) {
+            AY_TRY(ay::launch_f32_split_s2_gather(prev, pC, L.cin, batch, pH, pW, ctx->f_planes, L.plane_rows, st));
             ++ctx->launches;
+          } else {
+            AY_TRY(ay::launch_f32_split(prev, pC, L.cin, ay::padded_rows_f32(batch, pH, pW), ctx->f_split, st));
+            ++ctx->launches;
+            if (L.d.stride == 2) {
+              AY_TRY(ay::launch_f32_s2_gather(ctx->f_split, 2 * L.cin, batch, pH, pW, ctx->f_planes, L.plane_rows, st));
+              ++ctx->launches;
+            }
           }
           const int Wq = L.W + 2, taps = L.d.size * L.d.size;
           ay::ConvGemmParams g{};
@@ -961,7 +982,7 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
               g.b_col_off[gi] = pass == 1 ? L.ktot : 0;             // pass 1: A_hi x W_lo; pass 2: A_hi x W_hi
             }
           (void)taps;
-          g.BN = L.BN; g.num_stages = L.stages; g.nbuf = L.nbuf; g.units_per_stage = 1;
+          g.BN = L.BN; g.num_stages = L.stages; g.nbuf = L.nbuf; g.units_per_stage = L.units_per_stage;
           g.tf32_na = ctx->tf32_na;
           g.num_acc = std::min(16, 512 / (L.BN * g.tf32_na));
           if (g.num_acc > 1) g.num_acc &= ~1;
@@ -969,6 +990,12 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
           g.Hp = L.H + 2; g.Wp = Wq;
           g.bias = L.bias; g.leaky = L.d.leaky; g.cout = L.C;
           g.out_ptr = L.f_out; g.out_pitch = L.C;
+          if (L.fused_shortcut >= 0) {
+            const float* res = Ls[L.residual_src].f_out;
+            if (!res) { set_error("layer %d: residual source %d has no stored output", i, L.residual_src); return AY_ESTATE; }
+            g.out_ptr = Ls[L.fused_shortcut].f_out;
+            g.has_res = 1; g.res_ptr = res; g.res_pitch = L.C;
+          }
           g.err_flag = ctx->err_flag;
           g.pdl = 0;
           AY_TRY(ay::launch_conv_gemm(L.tmA, L.tmB, g, L.G, 2, ctx->num_sms, st));
@@ -1003,6 +1030,7 @@ int forward_f32(ay_ctx* ctx, const void* input, int in_kind, int batch, int src_
         }
         break;
       case AY_SHORTCUT:
+        if (L.fused_into_prev) break;                       // written by the previous convolution's epilogue
         AY_TRY(ay::launch_f32_add(prev, Ls[L.d.src[0]].f_out, ay::padded_rows_f32(batch, L.H, L.W) * L.C, L.f_out, st));
         ++ctx->launches;
         break;

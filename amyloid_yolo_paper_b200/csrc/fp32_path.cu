@@ -10,6 +10,8 @@
 // zeros the buffers were allocated with, so 3x3 taps and the ZeroPad2d of the stride-1 maxpool read zeros.
 #include "ay_common.h"
 
+#include <cstdlib>
+
 namespace ay {
 namespace {
 
@@ -43,6 +45,45 @@ __global__ void f32_prep_kernel(F32PrepParams p) {
     }
     float* o = p.out + (((size_t)n * (p.S + 2) + y + 1) * (p.S + 2) + x + 1) * 3;
     o[0] = v[0]; o[1] = v[1]; o[2] = v[2];
+  }
+}
+
+// First layer of the fp32 mode (3 input channels, 3x3, stride 1, up to 64 filters): one thread per output pixel, its 27
+// inputs in registers, the [27][Cout] weights in shared memory read four filters at a time as broadcasts.  The generic
+// kernel below spends this layer on scalar gathers with a division per element and on the unused half of its 64-filter tile
+// (3.8 ms of a 35 ms forward at B = 64).  Each output is one 27-term FMA chain plus the bias: K is too short to need the
+// compensated two-level sum.
+__global__ void __launch_bounds__(128) f32_first_conv_kernel(F32ConvParams p) {
+  __shared__ __align__(16) float ws[27 * 64];
+  __shared__ float bs[64];
+  for (int i = threadIdx.x; i < 27 * p.Cout; i += blockDim.x) ws[i] = __ldg(p.w + i);
+  for (int i = threadIdx.x; i < p.Cout; i += blockDim.x) bs[i] = __ldg(p.bias + i);
+  __syncthreads();
+  const int ox = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ox >= p.Wo) return;
+  const int oy = blockIdx.y, n = blockIdx.z;
+  const int Wq = p.W + 2;
+  float in[27];
+#pragma unroll
+  for (int kh = 0; kh < 3; ++kh) {
+    const float* row = p.in + (((size_t)n * (p.H + 2) + oy + kh) * Wq + ox) * p.in_pitch;   // padded (oy + kh, ox + kw)
+#pragma unroll
+    for (int j = 0; j < 9; ++j) in[kh * 9 + j] = __ldg(row + (j / 3) * p.in_pitch + (j % 3));
+  }
+  float* o = p.out + (((size_t)n * (p.Ho + 2) + oy + 1) * (p.Wo + 2) + ox + 1) * p.out_pitch;
+  for (int c = 0; c < p.Cout; c += 4) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 27; ++k) {
+      const float4 w = *reinterpret_cast<const float4*>(&ws[k * p.Cout + c]);
+      a0 = fmaf(in[k], w.x, a0); a1 = fmaf(in[k], w.y, a1); a2 = fmaf(in[k], w.z, a2); a3 = fmaf(in[k], w.w, a3);
+    }
+    float v[4] = {__fadd_rn(a0, bs[c]), __fadd_rn(a1, bs[c + 1]), __fadd_rn(a2, bs[c + 2]), __fadd_rn(a3, bs[c + 3])};
+    if (p.leaky) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) v[e] = v[e] > 0.f ? v[e] : __fmul_rn(v[e], act_slope(p.leaky));
+    }
+    *reinterpret_cast<float4*>(o + c) = make_float4(v[0], v[1], v[2], v[3]);
   }
 }
 
@@ -272,6 +313,35 @@ __global__ void f32_s2_gather_kernel(const float4* __restrict__ in, int P4, int 
   }
 }
 
+// The two passes above in one for stride-2 layers: raw fp32 rows in, [hi | lo] parity planes out (one read of the input
+// and one write of the planes instead of a split copy in between).
+__global__ void f32_split_s2_gather_kernel(const float4* __restrict__ in, int in_pitch4, int C4, int batch, int H, int W,
+                                           float4* __restrict__ planes, long long plane_rows) {
+  const int Ho = H / 2, Wo = W / 2;
+  const int Hq = Ho + 2, Wq = Wo + 2, Hp = H + 2, Wp = W + 2;
+  const long long per_plane = (long long)batch * Hq * Wq * C4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < 4 * per_plane;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int pl = (int)(i / per_plane);
+    long long r = i - (long long)pl * per_plane;
+    const int c = (int)(r % C4);
+    r /= C4;
+    const int b = (int)(r % Wq);
+    r /= Wq;
+    const int a = (int)(r % Hq);
+    const int n = (int)(r / Hq);
+    const int iy = 2 * (a - 1) + (pl >> 1), ix = 2 * (b - 1) + (pl & 1);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (iy >= 0 && iy < Hp && ix >= 0 && ix < Wp) v = __ldg(in + ((size_t)((size_t)n * Hp + iy) * Wp + ix) * in_pitch4 + c);
+    float4 h, l;
+    h.x = tf32_round(v.x); h.y = tf32_round(v.y); h.z = tf32_round(v.z); h.w = tf32_round(v.w);
+    l.x = __fsub_rn(v.x, h.x); l.y = __fsub_rn(v.y, h.y); l.z = __fsub_rn(v.z, h.z); l.w = __fsub_rn(v.w, h.w);
+    float4* o = planes + ((size_t)pl * plane_rows + ((size_t)n * Hq + a) * Wq + b) * 2 * C4;
+    o[c] = h;
+    o[C4 + c] = l;
+  }
+}
+
 __global__ void f32_dump_nchw_kernel(const float* __restrict__ in, int C, int batch, int H, int W,
                                      float* __restrict__ out) {
   const long long total = (long long)batch * C * H * W;
@@ -296,6 +366,12 @@ int launch_f32_prep(const F32PrepParams& p, cudaStream_t s) {
 }
 
 int launch_f32_conv(const F32ConvParams& p, cudaStream_t s) {
+  if (p.Cin == 3 && p.in_pitch == 3 && p.size == 3 && p.stride == 1 && p.Cout <= 64 && (p.Cout & 3) == 0 && (p.out_pitch & 3) == 0 &&
+      p.Ho <= 65535 && p.batch <= 65535 && !getenv("AY_F32_GENERIC_L0")) {
+    f32_first_conv_kernel<<<dim3((p.Wo + 127) / 128, p.Ho, p.batch), 128, 0, s>>>(p);
+    AY_CUDA(cudaGetLastError());
+    return AY_OK;
+  }
   const long long total = (long long)p.batch * p.Ho * p.Wo;
   const long long gx = (total + kBM - 1) / kBM;
   if (gx > 0x7fffffffLL) { set_error("fp32 conv: batch too large"); return AY_EINVAL; }
@@ -348,6 +424,16 @@ int launch_f32_s2_gather(const float* in, int pitch, int batch, int H, int W, fl
   const long long total = 4LL * batch * (H / 2 + 2) * (W / 2 + 2) * (pitch / 4);
   f32_s2_gather_kernel<<<grid_for32(total), 256, 0, s>>>(reinterpret_cast<const float4*>(in), pitch / 4, batch, H, W,
                                                          reinterpret_cast<float4*>(planes), plane_rows);
+  AY_CUDA(cudaGetLastError());
+  return AY_OK;
+}
+
+int launch_f32_split_s2_gather(const float* in, int in_pitch, int C, int batch, int H, int W, float* planes,
+                               long long plane_rows, cudaStream_t s) {
+  if ((C & 3) || (in_pitch & 3)) { set_error("f32 split: channels must be a multiple of 4"); return AY_EINVAL; }
+  const long long total = 4LL * batch * (H / 2 + 2) * (W / 2 + 2) * (C / 4);
+  f32_split_s2_gather_kernel<<<grid_for32(total), 256, 0, s>>>(reinterpret_cast<const float4*>(in), in_pitch / 4, C / 4, batch, H, W,
+                                                               reinterpret_cast<float4*>(planes), plane_rows);
   AY_CUDA(cudaGetLastError());
   return AY_OK;
 }

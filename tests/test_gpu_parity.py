@@ -389,12 +389,18 @@ def test_forward_fp32_mode_full_networks_vs_oracle(name, batch, dev):
         assert e32 <= 3 * FP32_TOL
     assert rel_max(got, ref32) <= FP32_TOL
     assert rel_max(got[..., 4:], ref32[..., 4:]) <= FP32_TOL
-    worst = 0.0
+    from amyloid_yolo_paper_b200 import _lib
+    worst, checked = 0.0, 0
     for i, dsc in enumerate(blocks[1:]):
         if dsc["type"] == "yolo":
             continue
-        worst = max(worst, rel_max(eng.layer_output(i, batch).cpu(), ref_layers[i]))
+        try:
+            worst = max(worst, rel_max(eng.layer_output(i, batch).cpu(), ref_layers[i]))
+            checked += 1
+        except _lib.EngineError as e:                   # a convolution whose [shortcut] is fused into its epilogue
+            assert "no stored output" in str(e) and blocks[1:][i + 1]["type"] == "shortcut", (i, str(e))
     assert worst <= FP32_TOL, "per-layer activations vs fp32 oracle: %.3e" % worst
+    assert checked >= len(blocks[1:]) * 2 // 3
     # same tiles through the caller's float contract (Darknet.forward): identical bits to the u8 entry
     y = m(x)
     assert np.array_equal(bits(y), bits(got))

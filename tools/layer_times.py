@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--tile", type=int, default=1536)
     ap.add_argument("--out", default="")
     ap.add_argument("--counters", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp16", "fp32"])
     args = ap.parse_args()
     import torch
     from amyloid_yolo_paper_b200 import _lib, synth
@@ -33,6 +34,7 @@ def main():
 
     dev = torch.device("cuda", 0)
     model = Darknet(ensure_cfg(args.net))
+    model.precision = args.precision
     synth.synthetic_state_dict(model, seed=0, conf_bias=-3.5)
     eng = model.engine(device=dev, max_batch=args.batch)
     B = args.batch
