@@ -150,6 +150,8 @@ class CAAEngine(Engine):
 def _axis_window(centre, size):
     """One axis of ``get256Img``: 256 pixels centred on ``centre`` when they fit strictly inside (the reference's
     comparisons are ``centre - 128 > 0`` and ``centre + 128 < size``), else the window flush with the near edge."""
+    if size < CROP:
+        raise ValueError("a %d-pixel tile has no 256-pixel window" % size)
     low_ok, high_ok = centre - CROP // 2 > 0, centre + CROP // 2 < size
     if low_ok and high_ok:
         return centre - CROP // 2, centre + CROP // 2

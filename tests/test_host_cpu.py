@@ -258,3 +258,25 @@ def test_slide_tiling_host_logic(tmp_path):
     assert crop.halve(np.full((5, 7, 3), 11, np.uint8)).shape == (2, 3, 3)
     with pytest.raises(ValueError):
         crop.detector_inputs(torch.zeros((10, 10, 3), dtype=torch.uint8), 0, 0, 1, 1)      # host tensor: no CPU path
+
+
+def test_caa_host_side_fails_loudly_without_gpu():
+    """The CAA filter's crop / network path has no CPU fallback either: host tensors are rejected, a missing GPU raises."""
+    from amyloid_yolo_paper_b200 import caa
+    tile = torch.zeros((600, 600, 3), dtype=torch.uint8)
+    with pytest.raises(ValueError):
+        caa.normalised_crops(tile, [(0, 256, 0, 256)], [0.5] * 3, [0.2] * 3)            # host tensor: no CPU path
+    with pytest.raises(ValueError):
+        caa.crop_window((10, 10, 5, 5), size=200)                                       # no 256-pixel window in a 200-pixel tile
+    assert caa.crop_window((0, 0, 10, 10), 600) == (0, 256, 0, 256)
+    assert caa.crop_window((590, 300, 10, 10), 600) == (344, 600, 177, 433)
+    net = caa.Net()
+    assert not net.training and net.precision == "fp32"
+    if not torch.cuda.is_available():
+        with pytest.raises(_lib.EngineUnavailable):
+            net(torch.zeros(1, 3, 256, 256))
+        with pytest.raises(_lib.EngineUnavailable):
+            caa.filterDetectionsByCAAModel(tile, torch.zeros((1, 7)), ["Cored", "CAA"], model=net,
+                                           norm={"mean": [0.5] * 3, "std": [0.2] * 3})
+    empty = caa.filterDetectionsByCAAModel(tile, torch.zeros((0, 7)), ["Cored", "CAA"], model=net, norm={"mean": [0.5] * 3, "std": [0.2] * 3})
+    assert empty.numel() == 0                                                           # nothing to classify: no engine needed
