@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libamyloid_yolo_b200.so")
 HEADER = os.path.join(os.path.dirname(HERE), "include", "amyloid_yolo.h")
-SOURCES = ["engine.cu", "conv_gemm_sm100.cu", "aux_kernels.cu", "fp32_path.cu", "nms.cu", "merge.cu"]
+SOURCES = ["engine.cu", "conv_gemm_sm100.cu", "first_conv_ts.cu", "aux_kernels.cu", "fp32_path.cu", "nms.cu", "merge.cu"]
 
 AY_CONV, AY_MAXPOOL, AY_UPSAMPLE, AY_ROUTE, AY_SHORTCUT, AY_YOLO, AY_LINEAR = range(7)
 AY_IN_F32_NCHW, AY_IN_U8_HWC = 0, 1

@@ -143,6 +143,18 @@ struct FirstConvParams {
   const float* bias; int cout; int leaky;
   void* out; int out_pitch; int Cp; int is_fp16;
 };
+// first convolution with the A operand built in tensor memory (first_conv_ts.cu)
+struct FirstConvTsParams {
+  const void* in; int in_kind; int batch; int S; int src_h, src_w;
+  const int* idx_y; const int* idx_x;      // nearest-resize source indices (u8 input)
+  const void* w_ts;                         // [32 x 32] 16-bit, K-major, canonical unswizzled core-matrix layout (2 KB)
+  const float* bias;                        // [32]
+  int leaky, is_fp16;
+  void* out_ptr; int out_pitch;             // output rows (unless plane_mode == 2)
+  int plane_mode, plane_packed; void* planes; long long plane_rows; int plane_pitch;   // as ConvGemmParams
+  unsigned int* err_flag;
+};
+int launch_first_conv_ts(const FirstConvTsParams& p, int num_sms, cudaStream_t s);
 int launch_first_conv(const FirstConvParams& p, cudaStream_t s);
 int launch_prep_input(const FirstConvParams& p, cudaStream_t s);   // p.out = [B,S+2,S+2,8] 16-bit
 int launch_s2_gather(const void* in, int in_pitch, int C8, int batch, int H, int W,

@@ -116,6 +116,8 @@ struct Layer {
   int impl = 0;                     // 0 none, 1 tcgen05 gemm
   bool first = false;               // 3-channel first layer: GEMM over the staged 8-channel input x8
   void* x8 = nullptr;               // [B, S+2, S+2, 8] 16-bit (first layer only)
+  void* w_ts = nullptr;             // first layer, A-in-TMEM kernel (first_conv_ts.cu): [32 x 32] 16-bit weights, core-matrix layout
+  bool l0_ts = false;
   void* w16 = nullptr;              // [cout_rows][ktot] 16-bit (gemm)
   float* w32 = nullptr;             // [cout][27] fp32 (first layer)
   float* bias = nullptr;            // [cout_rows]
@@ -717,6 +719,14 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       }
     }
     if (L.stages < 2) { set_error("layer %d: tile does not fit in shared memory", i); return AY_EINVAL; }
+    // first layer with <= 32 filters and a plain output, opt-in (AY_L0_TS=1): im2col rows built in tensor memory
+    // (first_conv_ts.cu).  Bit-compatible in the tests, but instruction-bound - 1 434 us against 1 123 for the staged
+    // path at B = 256 (profiles/r2_ab_l0_tmem.txt) - so the staged path stays the default.
+    if (L.first && cout_p == 32 && !L.is_head && L.fused_shortcut < 0 && L.up_consumer < 0 && (img_size & 1) == 0 &&
+        getenv("AY_L0_TS")) {
+      L.l0_ts = true;
+      AY_TRY(ay::dev_alloc(ctx, &L.w_ts, 32 * 32 * 2, true));
+    }
     AY_TRY(ay::dev_alloc(ctx, &L.w16, (size_t)L.cout_rows * L.ktot * 2, true));
     if (L.s2_packed) AY_TRY(ay::dev_alloc(ctx, &L.w16_ref, (size_t)L.cout_rows * 9 * L.cin_k * 2, true));
     AY_TRY(ay::dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), sizeof(float) * L.cout_rows, true));
@@ -838,6 +848,19 @@ extern "C" int ay_net_set_conv(ay_ctx* ctx, int layer, const float* w, const flo
     memcpy(b.data(), bias, sizeof(float) * cout);
     AY_CUDA(cudaMemcpy(L.w32, r.data(), r.size() * sizeof(float), cudaMemcpyHostToDevice));
     AY_CUDA(cudaMemcpy(L.w16, r16.data(), r16.size() * 2, cudaMemcpyHostToDevice));
+    if (L.l0_ts) {
+      // [filter n][k = (kh*3 + kw)*3 + c], K-major, as unswizzled 8 x 16-byte core matrices: K chunk k/8 of filter group n/8
+      // at ((n/8)*4 + k/8) * 128 bytes, row n%8 at 16 bytes, element k%8 at 2 bytes
+      std::vector<uint16_t> ts(32 * 32, 0);
+      for (int o = 0; o < cout; ++o)
+        for (int c = 0; c < 3; ++c)
+          for (int t = 0; t < 9; ++t) {
+            const int k = t * 3 + c;
+            ts[(size_t)(((o / 8) * 4 + k / 8) * 64 + (o % 8) * 8 + k % 8)] =
+                ay::to16((float)((double)w[((size_t)o * 3 + c) * 9 + t] / 255.0), ctx->is_fp16);
+          }
+      AY_CUDA(cudaMemcpy(L.w_ts, ts.data(), ts.size() * 2, cudaMemcpyHostToDevice));
+    }
     AY_CUDA(cudaMemcpy(L.bias, b.data(), sizeof(float) * L.cout_rows, cudaMemcpyHostToDevice));
   } else {
     std::vector<uint16_t> r((size_t)L.cout_rows * L.ktot, 0);
@@ -1074,6 +1097,19 @@ int run_conv(ay_ctx* ctx, int i, const void* input, int in_kind, int batch, int 
     p.out = target->ptr; p.out_pitch = target->pitch; p.Cp = target->Cp; p.is_fp16 = ctx->is_fp16;
     ++ctx->launches;
     if (ctx->use_ref) return ay::launch_first_conv(p, st);   // fp32 CUDA-core reference of this layer
+    if (L.l0_ts) {
+      ay::FirstConvTsParams t{};
+      t.in = input; t.in_kind = in_kind; t.batch = batch; t.S = ctx->img_size; t.src_h = src_h; t.src_w = src_w;
+      t.idx_y = ctx->idx_y; t.idx_x = ctx->idx_x; t.w_ts = L.w_ts; t.bias = L.bias; t.leaky = L.d.leaky; t.is_fp16 = ctx->is_fp16;
+      t.out_ptr = target->ptr; t.out_pitch = target->pitch;
+      if (L.plane_consumer >= 0) {
+        const Layer& Cn = Ls[L.plane_consumer];
+        t.plane_mode = L.plane_mode; t.planes = Cn.planes; t.plane_rows = Cn.plane_rows;
+        t.plane_packed = Cn.s2_packed ? 1 : 0; t.plane_pitch = target->Cp;
+      }
+      t.err_flag = ctx->err_flag;
+      return ay::launch_first_conv_ts(t, ctx->num_sms, st);
+    }
     p.out = L.x8;
     AY_TRY(ay::launch_prep_input(p, st));
   }

@@ -565,7 +565,7 @@ def test_pipeline_end_to_end_vs_oracle_chain(dev):
 
 
 @pytest.mark.parametrize("toggle", ["AY_NO_RESIDENT", "AY_NO_PACKED", "AY_NO_MBATCH", "AY_NO_UPFUSE", "AY_NO_HEADSTAGE",
-                                    "AY_ONE_UNIT", "AY_FULL_K", "AY_NO_PDL", "AY_NO_HEADFAST"])
+                                    "AY_ONE_UNIT", "AY_FULL_K", "AY_NO_PDL", "AY_NO_HEADFAST", "AY_L0_TS"])
 def test_forward_plan_variants_agree(toggle, dev):
     """Every planning shortcut of the convolution engine (resident weights, packed stride-2 operand, row-batched first
     layer, fused upsample, staged head stores, multi-unit stages) can be switched off at ay_net_build time; the plain
