@@ -23,6 +23,8 @@ def _worker(rank, world, port, n_tiles, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
+        from amyloid_yolo_paper_b200.sweep import warm_gather
+        warm_gather(n_tiles, 5, "cpu")                  # the untimed exchange of the sweep's shape (bench warm-up): no side effects
         lo, hi = shard_range(n_tiles, rank, world)
         rows, counts = pack_detections([_tile_detections(t) for t in range(lo, hi)])
         all_rows, all_counts = allgather_detections(rows, counts, n_tiles)
