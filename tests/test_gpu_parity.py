@@ -276,6 +276,33 @@ def test_forward_mini_vs_reference_golden(golden, dev):
                 assert eng.layer_impl(i) in (1, 2), "every conv must run a CUDA kernel (1 = tcgen05, 2 = first layer)"
 
 
+@pytest.mark.parametrize("name,batch", [("yolov3-custom", 2), ("yolov3-tiny", 3)])
+def test_forward_fp16_storage_vs_oracle(name, batch, dev):
+    """precision = "fp16" (the other 16-bit storage type of the engine: 10 mantissa bits instead of 7): RAW head outputs
+    vs the fp32 oracle, tighter than the bf16 bar; exercises the FP16 instances of the convolution, max-pool and decode
+    kernels (tiny: max-pools, 255-channel heads; custom: residual epilogues, parity planes, fused upsample)."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    cfg = ensure_cfg(name)
+    m, sd = _model(cfg, seed=1, conf_bias=-2.0)
+    m.precision = "fp16"
+    blocks = R.parse_cfg(cfg)
+    tiles = synth.synthetic_tiles(batch, size=640, seed=3)
+    x = torch.stack([R.preprocess_u8(t, 416) for t in tiles])
+    with torch.no_grad():
+        ref32, raw32 = R.darknet_forward(blocks, sd, x, return_raw_heads=True)
+    eng = m.engine(device=dev, max_batch=batch)
+    assert eng.precision == "fp16"
+    got = eng.forward_u8(torch.from_numpy(tiles)).cpu()
+    eng.check()
+    assert got.shape == ref32.shape and torch.isfinite(got).all()
+    err = raw_head_error(got, raw32, blocks)
+    print("fp16 storage, %s: raw heads rel err %.3e (bf16 bar %.0e)" % (name, err, BF16_TOL))
+    assert err <= BF16_TOL / 4, "raw head outputs vs fp32 oracle in fp16: %.3e" % err
+    y = m(x)                                             # float entry: same bits as the u8 entry
+    assert np.array_equal(bits(y), bits(got))
+
+
 @pytest.mark.parametrize("name,batch", [("yolov3-custom", 3), ("yolov3-tiny", 5)])
 def test_forward_full_networks_vs_oracle(name, batch, dev):
     """Decoded head outputs of the whole network vs the fp32 oracle (tolerance 2e-2, bf16 storage)
