@@ -41,7 +41,9 @@ class Net(nn.Module):
         self.classifier = nn.Sequential(nn.Linear(96 * 4 * 4, num_classes))
         self.train_loss_curve, self.dev_loss_curve, self.train_auprc, self.dev_auprc = [], [], [], []
         self.num_classes = num_classes
-        self.precision = precision          # "fp32" (default: the gate is a threshold on the logit), "bf16", "fp16"
+        # "fp32" (default: the gate is a threshold on the logit; measured 1e-6 from the reference's logits), "fp16" (the fast
+        # 16-bit tensor-core path at 1.3e-3), "bf16" (same speed, 1e-2)
+        self.precision = precision
         self._engine = None
         self._engine_key = None
         self.eval()
