@@ -626,6 +626,34 @@ def test_forward_plan_variants_agree(toggle, dev):
         assert np.array_equal(bits(base), bits(other)), "%s changes only data movement: results must be bit-identical" % toggle
 
 
+@pytest.mark.parametrize("toggle", ["AY_F32_TWO_PASS", "AY_F32_NO_RESFUSE", "AY_F32_GENERIC_L0"])
+def test_fp32_mode_plan_variants_agree(toggle, dev):
+    """The fusions of the fp32 accuracy mode can be switched off when the network is built: the separate split + gather passes
+    of stride-2 layers and the stand-alone [shortcut] add perform the same fp32 operations (bit-identical output), the generic
+    first-layer kernel sums in another order (1e-5)."""
+    from amyloid_yolo_paper_b200 import synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    cfg = ensure_cfg("yolov3-custom")
+    m, _ = _model(cfg, seed=3, conf_bias=-2.0, wh_gain=0.15)
+    m.precision = "fp32"
+    tiles = torch.from_numpy(synth.synthetic_tiles(1, size=416, seed=11))
+    base = m.engine(device=dev, max_batch=1).forward_u8(tiles).cpu()
+    m._engine = None
+    os.environ[toggle] = "1"
+    try:
+        eng2 = m.engine(device=dev, max_batch=1)
+        other = eng2.forward_u8(tiles).cpu()
+        eng2.check()
+    finally:
+        del os.environ[toggle]
+        m._engine = None
+    assert torch.isfinite(other).all()
+    if toggle == "AY_F32_GENERIC_L0":
+        assert rel_max(other, base) <= 1e-5
+    else:
+        assert np.array_equal(bits(other), bits(base)), "%s moves work between kernels without changing a rounding" % toggle
+
+
 @pytest.mark.gpu
 def test_detect_stream_equals_per_batch_detect(dev):
     """The streaming host path (one pipeline across batches, uneven sub-batches, ragged last batch, an empty batch)
