@@ -659,3 +659,30 @@ def test_slide_gather_and_detect_slide(dev):
             assert torch.equal(d.view(torch.int32), ref.view(torch.int32)), (r, c)
             n += len(d)
     assert n > 0
+
+
+# ------------------------------------------------------------------ the sweep's device-resident path on one GPU
+def test_sweep_device_resident_equals_detect(dev):
+    """sweep.sweep over device tiles (ragged last batch; results appended on the GPU, one read-back of the longest list) returns
+    the rows TileDetector.detect returns tile by tile, zero-padded; the host-tile path of the same call agrees."""
+    from amyloid_yolo_paper_b200 import sweep, synth
+    from amyloid_yolo_paper_b200.config import ensure_cfg
+    from amyloid_yolo_paper_b200.pipeline import TileDetector
+    m, _ = _model(ensure_cfg("yolov3-custom"), seed=1, conf_bias=-2.5, wh_gain=0.15)
+    det = TileDetector(m, conf_thres=0.8, nms_thres=0.4, merge_boxes=True, max_batch=2, cap=512, device=dev)
+    tiles = torch.from_numpy(synth.synthetic_tiles(5, size=640, seed=21))
+    tiles_d = tiles.to(dev)
+    want = det.detect(tiles_d)
+    rows, counts = sweep.sweep(det, lambda lo, hi: tiles_d[lo:hi], 5, 2)
+    assert rows.is_cuda and counts.tolist() == [0 if w is None else len(w) for w in want]
+    assert rows.shape[1] == max(1, max(counts.tolist()))
+    for t, w in enumerate(want):
+        k = int(counts[t])
+        if k:
+            assert torch.equal(rows[t, :k].cpu().view(torch.int32), w.view(torch.int32))
+        assert not bool(rows[t, k:].view(torch.int32).any())                    # padding rows are zero
+    rows_h, counts_h = sweep.sweep(det, lambda lo, hi: tiles[lo:hi].pin_memory(), 5, 2)
+    assert counts_h.cpu().tolist() == counts.tolist()
+    kk = rows.shape[1]
+    assert torch.equal(rows_h.cpu()[:, :kk].view(torch.int32), rows.cpu().view(torch.int32))
+    assert sum(counts.tolist()) > 0
