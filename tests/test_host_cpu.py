@@ -280,3 +280,20 @@ def test_caa_host_side_fails_loudly_without_gpu():
                                            norm={"mean": [0.5] * 3, "std": [0.2] * 3})
     empty = caa.filterDetectionsByCAAModel(tile, torch.zeros((0, 7)), ["Cored", "CAA"], model=net, norm={"mean": [0.5] * 3, "std": [0.2] * 3})
     assert empty.numel() == 0                                                           # nothing to classify: no engine needed
+
+
+def test_caa_load_reference_model_from_a_pickled_module_or_state_dict(tmp_path):
+    """core.py:432 pickles the whole nn.Module; load_reference_model takes its state_dict (or a saved state_dict)."""
+    from amyloid_yolo_paper_b200 import caa
+    from oracle.make_golden_caa import seeded_caa_state
+    state = seeded_caa_state(2)
+    src = caa.Net()
+    src.load_state_dict(state)
+    for obj, name in ((src, "module.pkl"), (state, "state.pkl")):
+        path = str(tmp_path / name)
+        torch.save(obj, path)
+        net = caa.load_reference_model(path, precision="fp16")
+        assert net.precision == "fp16" and not net.training
+        got = net.state_dict()
+        assert set(got) == set(state)
+        assert all(torch.equal(got[k], state[k]) for k in state)
