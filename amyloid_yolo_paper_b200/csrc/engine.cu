@@ -696,12 +696,13 @@ extern "C" int ay_net_build(ay_ctx* ctx, const ay_layer_desc* descs, int n_layer
       const int res_cap = (getenv("AY_RES_KB") ? atoi(getenv("AY_RES_KB")) : 128) * 1024;
       const bool try_res = L.cout_rows == L.BN && res_bytes <= res_cap && !getenv("AY_NO_RESIDENT");
       L.units_per_stage = 1;
+      const int stage_cap = (getenv("AY_STAGE_KB") ? atoi(getenv("AY_STAGE_KB")) : 56) * 1024;
       for (int pass = try_res ? 0 : 1; pass < 2 && L.stages == 0; ++pass) {
         const int rb = pass == 0 ? res_bytes : 0;
         const int unit_bytes = ay::conv_gemm_stage_bytes(L.BN, L.G, L.a_rows, rb > 0);
         int best_u = 0, best_st = 0, best_nb = 0;
         for (int u = 1; u <= units; ++u) {
-          if (units % u != 0 || (u > 1 && (u * unit_bytes > 56 * 1024 || getenv("AY_ONE_UNIT")))) continue;
+          if (units % u != 0 || (u > 1 && (u * unit_bytes > stage_cap || getenv("AY_ONE_UNIT")))) continue;
           int st = 0, nb = 0;
           ay::conv_gemm_pick_smem(L.BN, L.G, L.a_rows, rb, u, ay::kConvEpilogueWarps * L.head_stage_bytes, &st, &nb);
           if (st >= 3 && (u == 1 || nb == 2)) { best_u = u; best_st = st; best_nb = nb; }
